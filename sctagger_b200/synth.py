@@ -1,0 +1,151 @@
+"""Seeded synthetic inputs for the `match_trie` hot path.
+
+Barcodes: B distinct 16-mers, i.i.d. uniform over ACGT, written `barcode\\tcount`.
+Segments: rows `read{i}\\t{d}\\t{loc}\\t{seg}` in the format `extract_lr_bc` writes
+(reference scTagger.py:317-320) and `read_long_reads` parses (scTagger.py:602-628).
+
+Everything is vectorised numpy so that 10 M segments are generated in seconds; the
+generator is deterministic in (seed, n, B).  Two output forms:
+  * text files (gz or plain) for the CLI / reference harness,
+  * in-memory arrays (concatenated segment bytes + int32/int64 offsets) for the C-ABI.
+"""
+from __future__ import annotations
+
+import gzip
+import numpy as np
+
+ACGT = np.frombuffer(b"ACGT", dtype=np.uint8)
+_COMP = np.arange(256, dtype=np.uint8)
+_COMP[ord("A")], _COMP[ord("C")], _COMP[ord("G")], _COMP[ord("T")] = ord("T"), ord("G"), ord("C"), ord("A")
+
+# seeds fixed by SURVEY.md §8(d)
+SEEDS = {"cfg1": 1001, "cfg2": 1002, "cfg3": 1003, "cfg4": 1003, "cfg5": 1005}
+
+
+def make_barcodes(n_barcodes: int, seed: int, bl: int = 16) -> np.ndarray:
+    """(B, bl) uint8 ASCII matrix of distinct random barcodes, generation order = file order = bid."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((0, bl), dtype=np.uint8)
+    seen = set()
+    while out.shape[0] < n_barcodes:
+        need = n_barcodes - out.shape[0]
+        cand = ACGT[rng.integers(0, 4, size=(need + 16, bl))]
+        keep = []
+        for row in cand:
+            k = row.tobytes()
+            if k not in seen:
+                seen.add(k)
+                keep.append(row)
+                if len(keep) == need:
+                    break
+        if keep:
+            out = np.concatenate([out, np.stack(keep)], axis=0)
+    return out
+
+
+def barcode_counts(n_barcodes: int, seed: int) -> np.ndarray:
+    rng = np.random.default_rng(seed + 7919)
+    return rng.integers(1, 1001, size=n_barcodes)
+
+
+def make_segments(barcodes: np.ndarray, n_segments: int, seed: int):
+    """Return (seg_bytes uint8[sum len], offsets int64[n+1]).
+
+    seg = L(3 random) + core + R(random) ; core = mutated barcode (p=.9) or random 16-mer (p=.1);
+    total length 22 (p=.9) or U[23,28] (p=.1); reverse-complemented with p=.5.  ACGT only.
+    """
+    rng = np.random.default_rng(seed + 104729)
+    B, bl = barcodes.shape
+    n = n_segments
+    from_bc = rng.random(n) < 0.9
+    which = rng.integers(0, B, size=n)
+    n_edits = rng.choice(5, size=n, p=[0.50, 0.25, 0.12, 0.08, 0.05])
+    n_edits[~from_bc] = 0
+    tot_len = np.where(rng.random(n) < 0.9, 22, rng.integers(23, 29, size=n)).astype(np.int64)
+    do_rc = rng.random(n) < 0.5
+
+    # core as a padded matrix (bl + 4 wide: up to 4 insertions)
+    W = bl + 4
+    core = np.zeros((n, W), dtype=np.uint8)
+    core[:, :bl] = barcodes[which]
+    rnd_core = ACGT[rng.integers(0, 4, size=(n, bl))]
+    core[~from_bc, :bl] = rnd_core[~from_bc]
+    core_len = np.full(n, bl, dtype=np.int64)
+    cols = np.arange(W)[None, :]
+    for e in range(4):
+        act = n_edits > e
+        kind = rng.integers(0, 3, size=n)  # 0 sub, 1 ins, 2 del
+        u = rng.random(n)
+        newb = ACGT[rng.integers(0, 4, size=n)]
+        # substitution at pos in [0, len)
+        m = act & (kind == 0)
+        pos = np.minimum((u * core_len).astype(np.int64), core_len - 1)
+        idx = np.nonzero(m)[0]
+        core[idx, pos[idx]] = newb[idx]
+        # insertion before pos in [0, len]
+        m = act & (kind == 1)
+        idx = np.nonzero(m)[0]
+        if idx.size:
+            p = np.minimum((u[idx] * (core_len[idx] + 1)).astype(np.int64), core_len[idx])
+            sub = core[idx]
+            src = np.where(cols > p[:, None], cols - 1, cols)
+            sub = np.take_along_axis(sub, src, axis=1)
+            sub[np.arange(idx.size), p] = newb[idx]
+            core[idx] = sub
+            core_len[idx] += 1
+        # deletion at pos in [0, len)
+        m = act & (kind == 2) & (core_len > 1)
+        idx = np.nonzero(m)[0]
+        if idx.size:
+            p = np.minimum((u[idx] * core_len[idx]).astype(np.int64), core_len[idx] - 1)
+            sub = core[idx]
+            src = np.where(cols >= p[:, None], np.minimum(cols + 1, W - 1), cols)
+            sub = np.take_along_axis(sub, src, axis=1)
+            core[idx] = sub
+            core_len[idx] -= 1
+
+    tot_len = np.maximum(tot_len, core_len + 3)
+    Lmax = int(tot_len.max())
+    seg = ACGT[rng.integers(0, 4, size=(n, Lmax))]  # random fill: L and R come from here
+    # place the core at offset 3
+    c = np.arange(Lmax)[None, :]
+    in_core = (c >= 3) & (c < 3 + core_len[:, None])
+    core_pad = np.zeros((n, Lmax), dtype=np.uint8)
+    core_pad[:, 3:3 + W] = core[:, : max(0, min(W, Lmax - 3))]
+    seg = np.where(in_core, core_pad, seg)
+    # reverse-complement in place (within each row's own length)
+    ridx = np.nonzero(do_rc)[0]
+    if ridx.size:
+        sub = seg[ridx]
+        ln = tot_len[ridx]
+        src = np.clip(ln[:, None] - 1 - c, 0, Lmax - 1)
+        sub = _COMP[np.take_along_axis(sub, src, axis=1)]
+        seg[ridx] = sub
+    valid = c < tot_len[:, None]
+    seg_bytes = seg[valid]  # row-major flatten keeps per-row order
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(tot_len, out=offsets[1:])
+    return np.ascontiguousarray(seg_bytes), offsets
+
+
+def _open_w(path):
+    return gzip.open(path, "wb", compresslevel=1) if str(path).endswith(".gz") else open(path, "wb")
+
+
+def write_barcodes(path, barcodes: np.ndarray, seed: int):
+    counts = barcode_counts(barcodes.shape[0], seed)
+    with _open_w(path) as f:
+        f.write(b"".join(row.tobytes() + b"\t%d\n" % c for row, c in zip(barcodes, counts)))
+
+
+def write_segments(path, seg_bytes: np.ndarray, offsets: np.ndarray, first_index: int = 0):
+    sb = seg_bytes.tobytes()
+    with _open_w(path) as f:
+        buf = []
+        for i in range(offsets.shape[0] - 1):
+            s = sb[offsets[i]:offsets[i + 1]]
+            buf.append(b"read%d\t0\t0\t%s\n" % (first_index + i, s))
+            if len(buf) >= 65536:
+                f.write(b"".join(buf))
+                buf = []
+        f.write(b"".join(buf))
