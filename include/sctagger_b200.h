@@ -1,0 +1,118 @@
+/*
+ * sctagger_b200 — C ABI of the B200-native `match_trie` hot path of vpc-ccg/scTagger.
+ *
+ * The reference has no FFI: its in-process seam for this path is the Python call
+ *     run_get_matches_prefix(max_error, threads) -> dict[rid] -> (e, {(bid, strand)})      reference scTagger.py:688-716
+ * with its inputs in module globals (barcodes, lr_segs, lr_segs_idxs; scTagger.py:519-523, filled by
+ * read_sr_barcodes scTagger.py:631-640 and read_long_reads scTagger.py:602-628).  The entry points below are what a
+ * ctypes binding of that seam needs (see INTEGRATION.md for the stub a maintainer would add):
+ *
+ *   sct_create   <- the globals `barcodes`/`barcodes_rc` + the (max_error, threads, -bl, -m) arguments
+ *                   (scTagger.py:631-640, 758-768); builds the device pattern table once.
+ *   sct_match    <- run_get_matches_prefix (scTagger.py:688-716): all segments against all barcodes and their
+ *                   reverse complements; per segment the minimum edit distance, the number of tied patterns and the
+ *                   tied pattern ids in the order the reference prints them (scTagger.py:789).
+ *   sct_destroy  <- process exit.
+ *
+ * Plain pointers and sizes only; every function returns 0 on success or a negative SCT_E_* code, and never throws.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with SCT_E_CUDA.
+ * One handle drives one GPU; calls on different handles may run concurrently from different host threads (ctypes
+ * releases the GIL), calls on one handle must be serialised by the caller.
+ */
+#ifndef SCTAGGER_B200_H
+#define SCTAGGER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCT_OK            0
+#define SCT_E_ARG        -1   /* invalid argument (the reference would raise AssertionError, scTagger.py:140-143, 760-761) */
+#define SCT_E_CUDA       -2   /* CUDA runtime error / no device */
+#define SCT_E_NOMEM      -3   /* host or device allocation failed */
+#define SCT_E_UNSUPPORTED -4  /* parameter combination outside the implemented range (see sct_create) */
+#define SCT_E_STATE      -5   /* call sequence error (e.g. results requested before a run) */
+
+typedef struct sct_handle sct_handle;
+
+/* Number of visible CUDA devices (0 if none or if the runtime cannot be initialised). */
+int sct_device_count(void);
+
+/* Thread-local message describing the last error returned on this thread. */
+const char *sct_last_error(void);
+
+/*
+ * barcodes: n_barcodes * barcode_length bytes, file order = barcode id (scTagger.py:638).  Bytes other than upper-case
+ *   ACGT are scored as 'A' (map_char, scTagger.py:512-516) and kept as they are by the reverse complement
+ *   (rev_compl, scTagger.py:148-156).
+ * max_error: -mr.  Requires barcode_length > max_error >= 0 (scTagger.py:143).
+ * threads:   the reference's -t.  It fixes k = min{k : 4^k >= threads} (scTagger.py:689-697), which decides where a
+ *   match may start in segments holding non-ACGT bytes.  Requires barcode_length-max_error > k.
+ * mem_gb:    -m; sizes the streamed chunks (pinned staging + device buffers), > 0.
+ * Implemented range: barcode_length <= 32; the bit-parallel kernels cover barcode_length <= 16 and max_error <= 3,
+ *   anything else runs on the (slower, exact) dynamic-programming kernel.
+ */
+int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t barcode_length, int32_t max_error,
+               int32_t threads, double mem_gb, sct_handle **out);
+
+int sct_destroy(sct_handle *h);
+
+/*
+ * seg_bytes / seg_offsets: the concatenated segment bytes and n+1 offsets (lr_segs / lr_segs_idxs of
+ *   scTagger.py:617-626), in HOST memory, owned by the caller for the duration of the call.
+ * Outputs (host memory, caller-allocated, n entries unless noted):
+ *   min_ed[r]      minimum edit distance, or -1 when no pattern is within max_error (the reference then writes no row)
+ *   n_ties[r]      number of (barcode, strand) patterns at that minimum
+ *   tie_offsets    n+1 entries; ties of segment r are tie_ids[tie_offsets[r] .. tie_offsets[r+1])
+ *   *tie_ids       library-owned buffer, valid until the next sct_match / sct_destroy on this handle;
+ *                  id = (barcode_index << 1) | strand, strand 1 = forward, 0 = reverse complement, ascending — the
+ *                  sorted((bid, strand)) order of scTagger.py:789
+ *   *n_tie_ids     = tie_offsets[n]
+ * The call streams the segments through the GPU in chunks sized from mem_gb (pinned double-buffered async copies).
+ */
+int sct_match(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n,
+              int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets, const int32_t **tie_ids, int64_t *n_tie_ids);
+
+/*
+ * Device-resident variant used by bench.py's `value` leg: sct_stage copies one batch (it must fit one chunk) to the
+ * GPU, sct_run_staged runs the kernels on the resident batch (results stay on the device) and reports the device
+ * time of the whole pass and of the dominant match kernel, measured with CUDA events on the launching stream;
+ * sct_fetch_staged copies the results of the last run to the host with the sct_match output conventions.
+ */
+int sct_stage(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n);
+int sct_run_staged(sct_handle *h, float *pass_ms, float *match_kernel_ms);
+int sct_fetch_staged(sct_handle *h, int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets,
+                     const int32_t **tie_ids, int64_t *n_tie_ids);
+
+/* Counters of the last sct_match / sct_run_staged on this handle: [0] kernel launches, [1] segments on the
+ * bit-parallel fast path, [2] segments on the generic path (non-ACGT bytes, > 32 bases, or tie-list overflow
+ * re-runs), [3] host->device bytes, [4] device->host bytes, [5] chunks, [6] segments on the DP kernel, [7] reserved. */
+int sct_stats(sct_handle *h, int64_t stats[8]);
+
+/*
+ * Tuning / test hooks (set before the first sct_match / sct_stage):
+ *   "chunk_segments", "chunk_bytes"       override the chunk sizing derived from mem_gb
+ *   "tie_capacity_per_segment"            initial size of the device tie buffer (it grows and the pass is redone if short)
+ *   "path"                                0 = automatic, 1 = force the generic bit-parallel kernel, 2 = force the DP kernel
+ */
+int sct_set_option(sct_handle *h, const char *key, int64_t value);
+
+/* Largest batch (segments / bytes) sct_stage accepts with the handle's chunk sizing. */
+int sct_chunk_capacity(sct_handle *h, int64_t *max_segments, int64_t *max_bytes);
+
+/*
+ * INT32 ALU roofline denominator: runs a register-only kernel of independent LOP3 / IADD3 chains on
+ * every SM and reports lane-operations per second (best of `repeats`).  mode 0 = LOP3 only (ALU pipe),
+ * 1 = IADD3 only, 2 = LOP3 + IMAD mix (ALU + FMA pipes).
+ */
+int sct_measure_int32_peak(int device, int mode, int repeats, double *lane_ops_per_s);
+
+/* Wipe L2 by overwriting a buffer larger than it (used between timed bench iterations). */
+int sct_flush_l2(sct_handle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

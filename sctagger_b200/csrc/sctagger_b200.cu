@@ -1,0 +1,673 @@
+// Host side of libsctagger_b200.so: the C ABI of include/sctagger_b200.h around the kernels of match_kernels.cuh.
+// Replaces run_get_matches_prefix (reference scTagger.py:688-716): instead of forking one worker per DNA prefix that
+// rebuilds a trie over all reads, the reads are streamed through the GPU in chunks (pinned, double-buffered, one CUDA
+// stream per buffer) and every chunk is one pass of: prep -> match (fast / generic / overflow re-run | dp) -> finalize.
+// No PyTorch, no CPU fallback: every entry point fails with SCT_E_CUDA when there is no device.
+#include "match_kernels.cuh"
+#include "../../include/sctagger_b200.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace sct;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CUDA_TRY(x)                                                                                              \
+    do {                                                                                                         \
+        cudaError_t e_ = (x);                                                                                    \
+        if (e_ != cudaSuccess)                                                                                   \
+            return fail(e_ == cudaErrorMemoryAllocation ? SCT_E_NOMEM : SCT_E_CUDA, "%s: %s (%s:%d)", #x,        \
+                        cudaGetErrorString(e_), __FILE__, __LINE__);                                             \
+    } while (0)
+#define TRY(x)                  \
+    do {                        \
+        int rc_ = (x);          \
+        if (rc_ != SCT_OK) return rc_; \
+    } while (0)
+
+inline int map_char(uint8_t c) { return c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : 0; }   // scTagger.py:512-516
+inline uint8_t comp_char(uint8_t c) {                                                          // scTagger.py:148-152
+    return c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : c;
+}
+inline bool is_acgt(uint8_t c) { return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }
+
+template <class T>
+void dev_free(T *&p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+template <class T>
+void host_free(T *&p) {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+}
+
+struct Slot {
+    int64_t cap_segs = 0, cap_bytes = 0;
+    unsigned long long tie_cap = 0;
+    // pinned host staging
+    uint8_t *h_bytes = nullptr;
+    long long *h_off = nullptr;
+    int *h_min = nullptr, *h_nt = nullptr;
+    long long *h_toff = nullptr;
+    int *h_ties = nullptr;
+    Counters *h_ctr = nullptr;
+    long long *h_total = nullptr;
+    // device
+    uint8_t *d_bytes = nullptr, *d_colinfo = nullptr, *d_rec = nullptr, *d_segflag = nullptr;
+    long long *d_off = nullptr;
+    int *d_fast = nullptr, *d_gen = nullptr, *d_ovf = nullptr, *d_dp = nullptr;
+    Counters *d_ctr = nullptr;
+    int *d_min = nullptr, *d_nt = nullptr;
+    unsigned int *d_tstart = nullptr;
+    int *d_tiebuf = nullptr, *d_tieout = nullptr;
+    long long *d_toff = nullptr, *d_bsums = nullptr, *d_total = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_k0 = nullptr, ev_k1 = nullptr, ev_end = nullptr;
+    // in flight
+    int64_t n = 0, nbytes = 0, first = 0;
+    bool busy = false;
+};
+
+}  // namespace
+
+struct sct_handle {
+    int device = 0;
+    int B = 0, bl = 0, K = 0, threads = 0, kpre = 0;
+    double mem_gb = 16.0;
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    uint32_t *d_tabF = nullptr, *d_tabR = nullptr;
+    uint8_t *d_patF = nullptr, *d_patR = nullptr;
+    int n_tiles = 0;
+    bool clean_barcodes = true, use_dp = false, fast_ok = false;
+    int path_override = 0;       // 0 auto, 1 force generic, 2 force dp
+    size_t fast_smem = 0;
+    int64_t chunk_segs = 0, chunk_bytes = 0;
+    int tie_per_seg = 8;
+    uint32_t *d_ovf_scratch = nullptr;
+    int ovf_blocks = 16, ovf_cap = 0;
+    uint8_t *d_flush = nullptr;
+    size_t flush_bytes = 256u << 20;
+    Slot slot[2];
+    std::vector<int32_t> ties_host;
+    int64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool staged = false, staged_ran = false;
+};
+
+namespace {
+
+int free_slot(Slot &s) {
+    host_free(s.h_bytes); host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
+    host_free(s.h_ties); host_free(s.h_ctr); host_free(s.h_total);
+    dev_free(s.d_bytes); dev_free(s.d_colinfo); dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off);
+    dev_free(s.d_fast); dev_free(s.d_gen); dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_ctr);
+    dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart); dev_free(s.d_tiebuf); dev_free(s.d_tieout);
+    dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_total);
+    s.cap_segs = s.cap_bytes = 0;
+    s.tie_cap = 0;
+    return SCT_OK;
+}
+
+int alloc_ties(Slot &s, unsigned long long cap) {
+    dev_free(s.d_tiebuf);
+    dev_free(s.d_tieout);
+    host_free(s.h_ties);
+    s.tie_cap = 0;
+    CUDA_TRY(cudaMalloc(&s.d_tiebuf, cap * sizeof(int)));
+    CUDA_TRY(cudaMalloc(&s.d_tieout, cap * sizeof(int)));
+    CUDA_TRY(cudaMallocHost(&s.h_ties, cap * sizeof(int)));
+    s.tie_cap = cap;
+    return SCT_OK;
+}
+
+int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
+    if (!s.stream) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreate(&s.ev_start));
+        CUDA_TRY(cudaEventCreate(&s.ev_k0));
+        CUDA_TRY(cudaEventCreate(&s.ev_k1));
+        CUDA_TRY(cudaEventCreate(&s.ev_end));
+        CUDA_TRY(cudaMallocHost(&s.h_ctr, sizeof(Counters)));
+        CUDA_TRY(cudaMallocHost(&s.h_total, sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_ctr, sizeof(Counters)));
+        CUDA_TRY(cudaMalloc(&s.d_total, sizeof(long long)));
+    }
+    if (segs > s.cap_segs) {
+        const int64_t c = std::max<int64_t>(segs, 1024);
+        host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
+        dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off); dev_free(s.d_fast); dev_free(s.d_gen);
+        dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart);
+        dev_free(s.d_toff); dev_free(s.d_bsums);
+        s.cap_segs = 0;
+        CUDA_TRY(cudaMallocHost(&s.h_off, (c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMallocHost(&s.h_min, c * sizeof(int)));
+        CUDA_TRY(cudaMallocHost(&s.h_nt, c * sizeof(int)));
+        CUDA_TRY(cudaMallocHost(&s.h_toff, (c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_rec, (size_t)c * REC_BYTES));
+        CUDA_TRY(cudaMalloc(&s.d_segflag, (size_t)c));
+        CUDA_TRY(cudaMalloc(&s.d_off, (c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_fast, c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_gen, c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_ovf, c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_dp, c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_min, c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_nt, c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_tstart, c * sizeof(unsigned int)));
+        CUDA_TRY(cudaMalloc(&s.d_toff, (c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_bsums, ((c + SCAN_BLOCK - 1) / SCAN_BLOCK + 1) * sizeof(long long)));
+        s.cap_segs = c;
+        const unsigned long long want = (unsigned long long)c * h->tie_per_seg + 4096;
+        if (want > s.tie_cap) TRY(alloc_ties(s, want));
+    }
+    if (bytes > s.cap_bytes) {
+        const int64_t c = std::max<int64_t>(bytes, 4096);
+        host_free(s.h_bytes);
+        dev_free(s.d_bytes);
+        dev_free(s.d_colinfo);
+        s.cap_bytes = 0;
+        CUDA_TRY(cudaMallocHost(&s.h_bytes, (size_t)c + 64));
+        CUDA_TRY(cudaMalloc(&s.d_bytes, (size_t)c + 64));
+        CUDA_TRY(cudaMalloc(&s.d_colinfo, (size_t)c + 64));
+        s.cap_bytes = c;
+    }
+    return SCT_OK;
+}
+
+MatchParams make_params(sct_handle *h, Slot &s) {
+    MatchParams p;
+    p.tabF = h->d_tabF;
+    p.tabR = h->d_tabR;
+    p.n_tiles = h->n_tiles;
+    p.n_barcodes = h->B;
+    p.bl = h->bl;
+    p.seg_bytes = s.d_bytes;
+    p.seg_off = s.d_off;
+    p.rec = s.d_rec;
+    p.colinfo = s.d_colinfo;
+    p.segflag = s.d_segflag;
+    p.fast_list = s.d_fast;
+    p.gen_list = s.d_gen;
+    p.ovf_list = s.d_ovf;
+    p.ctr = s.d_ctr;
+    p.min_ed = s.d_min;
+    p.n_ties = s.d_nt;
+    p.tie_start = s.d_tstart;
+    p.tie_buf = s.d_tiebuf;
+    p.tie_cap = s.tie_cap;
+    p.ovf_scratch = h->d_ovf_scratch;
+    p.ovf_scratch_cap = h->ovf_cap;
+    return p;
+}
+
+template <int K>
+int launch_match(sct_handle *h, Slot &s, const MatchParams &p, bool fast) {
+    if (fast) {
+        if (h->bl == 16) {
+            CUDA_TRY(cudaFuncSetAttribute(match_fast_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fast_smem));
+            match_fast_kernel<K, true><<<h->sm_count, FAST_THREADS, h->fast_smem, s.stream>>>(p);
+        } else {
+            CUDA_TRY(cudaFuncSetAttribute(match_fast_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fast_smem));
+            match_fast_kernel<K, false><<<h->sm_count, FAST_THREADS, h->fast_smem, s.stream>>>(p);
+        }
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
+    }
+    match_generic_kernel<K><<<h->sm_count * 4, GEN_THREADS, 0, s.stream>>>(p, 0);
+    CUDA_TRY(cudaGetLastError());
+    match_generic_kernel<K><<<h->ovf_blocks, GEN_THREADS, 0, s.stream>>>(p, 1);
+    CUDA_TRY(cudaGetLastError());
+    return SCT_OK;
+}
+
+// Enqueue one full pass over the n segments resident in slot s (no host synchronisation).
+int enqueue_pass(sct_handle *h, Slot &s, int64_t n) {
+    const int path = h->path_override ? h->path_override : (h->use_dp ? 2 : (h->fast_ok ? 0 : 1));
+    MatchParams p = make_params(h, s);
+    CUDA_TRY(cudaEventRecord(s.ev_start, s.stream));
+    CUDA_TRY(cudaMemsetAsync(s.d_ctr, 0, sizeof(Counters), s.stream));
+    int launches = 0;
+    if (n > 0) {
+        prep_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.d_bytes, s.d_off, (int)n, h->bl, h->K, h->kpre, path,
+                                                                     s.d_rec, s.d_colinfo, s.d_segflag, s.d_fast, s.d_gen,
+                                                                     s.d_dp, s.d_ctr, s.d_min, s.d_nt);
+        CUDA_TRY(cudaGetLastError());
+        ++launches;
+        CUDA_TRY(cudaEventRecord(s.ev_k0, s.stream));
+        if (path == 2) {
+            DpParams q;
+            q.patF = h->d_patF;
+            q.patR = h->d_patR;
+            q.n_barcodes = h->B;
+            q.bl = h->bl;
+            q.K = h->K;
+            q.kpre = h->kpre;
+            match_dp_kernel<<<h->sm_count * 8, 128, 0, s.stream>>>(p, q, s.d_dp);
+            CUDA_TRY(cudaGetLastError());
+            CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
+            ++launches;
+        } else {
+            const bool fast = path == 0;
+            switch (h->K) {
+                case 0: TRY(launch_match<0>(h, s, p, fast)); break;
+                case 1: TRY(launch_match<1>(h, s, p, fast)); break;
+                case 2: TRY(launch_match<2>(h, s, p, fast)); break;
+                default: TRY(launch_match<3>(h, s, p, fast)); break;
+            }
+            if (!fast) CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
+            launches += fast ? 3 : 2;
+        }
+        const int nb = (int)((n + SCAN_BLOCK - 1) / SCAN_BLOCK);
+        scan_block_sums<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums);
+        CUDA_TRY(cudaGetLastError());
+        scan_block_prefix<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total);
+        CUDA_TRY(cudaGetLastError());
+        scan_gather<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums, s.d_tstart, s.d_tiebuf, s.d_toff, s.d_tieout);
+        CUDA_TRY(cudaGetLastError());
+        launches += 3;
+    } else {
+        CUDA_TRY(cudaEventRecord(s.ev_k0, s.stream));
+        CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.d_total, 0, sizeof(long long), s.stream));
+    }
+    CUDA_TRY(cudaEventRecord(s.ev_end, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_total, s.d_total, sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    h->stats[0] += launches;
+    return SCT_OK;
+}
+
+// Wait for the pass in slot s; if the bump-allocated tie buffer was too small, grow it and redo the pass.
+int complete_pass(sct_handle *h, Slot &s) {
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        if (s.h_ctr->tie_cursor <= s.tie_cap) {
+            h->stats[1] += s.h_ctr->n_fast;
+            h->stats[2] += s.h_ctr->n_gen + s.h_ctr->n_ovf;
+            h->stats[6] += s.h_ctr->n_dp;
+            return SCT_OK;
+        }
+        const unsigned long long need = s.h_ctr->tie_cursor + 4096;
+        TRY(alloc_ties(s, need));
+        TRY(enqueue_pass(h, s, s.n));
+    }
+    return fail(SCT_E_STATE, "tie buffer did not converge");
+}
+
+// Copy chunk [first, first+n) of the caller's arrays into the slot's pinned staging and start H2D + pass.
+int start_chunk(sct_handle *h, Slot &s, const uint8_t *seg_bytes, const int64_t *off, int64_t first, int64_t n) {
+    const int64_t b0 = off[first], nbytes = off[first + n] - b0;
+    TRY(ensure_slot(h, s, n, nbytes));
+    if (nbytes > 0) memcpy(s.h_bytes, seg_bytes + b0, (size_t)nbytes);
+    for (int64_t i = 0; i <= n; ++i) s.h_off[i] = off[first + i] - b0;
+    s.n = n;
+    s.nbytes = nbytes;
+    s.first = first;
+    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
+    h->stats[3] += nbytes + (n + 1) * (int64_t)sizeof(long long);
+    h->stats[5] += 1;
+    TRY(enqueue_pass(h, s, n));
+    s.busy = true;
+    return SCT_OK;
+}
+
+// Bring the results of slot s back and append them to the caller's arrays.
+int fetch_results(sct_handle *h, Slot &s, int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets, int64_t out_first,
+                  int64_t tie_base, int64_t *n_new_ties) {
+    const int64_t n = s.n;
+    const long long total = n > 0 ? *s.h_total : 0;
+    if (n > 0) {
+        CUDA_TRY(cudaMemcpyAsync(s.h_min, s.d_min, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(s.h_nt, s.d_nt, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(s.h_toff, s.d_toff, (size_t)(n + 1) * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+        if (total > 0)
+            CUDA_TRY(cudaMemcpyAsync(s.h_ties, s.d_tieout, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        h->stats[4] += n * 8 + (n + 1) * 8 + total * 4;
+        memcpy(min_ed + out_first, s.h_min, (size_t)n * sizeof(int));
+        memcpy(n_ties + out_first, s.h_nt, (size_t)n * sizeof(int));
+        for (int64_t i = 0; i < n; ++i) tie_offsets[out_first + i] = tie_base + s.h_toff[i];
+        if (total > 0) h->ties_host.insert(h->ties_host.end(), s.h_ties, s.h_ties + total);
+    }
+    *n_new_ties = total;
+    s.busy = false;
+    return SCT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sct_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char *sct_last_error(void) { return g_err.c_str(); }
+
+int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t barcode_length, int32_t max_error,
+               int32_t threads, double mem_gb, sct_handle **out) {
+    if (!out) return fail(SCT_E_ARG, "out is NULL");
+    *out = nullptr;
+    if (!barcodes && n_barcodes > 0) return fail(SCT_E_ARG, "barcodes is NULL");
+    if (n_barcodes < 0) return fail(SCT_E_ARG, "n_barcodes < 0");
+    if (!(mem_gb > 0)) return fail(SCT_E_ARG, "mem must be > 0 (scTagger.py:141)");
+    if (!(barcode_length > 0)) return fail(SCT_E_ARG, "barcode_length must be > 0 (scTagger.py:142)");
+    if (!(barcode_length > max_error && max_error >= 0))
+        return fail(SCT_E_ARG, "need barcode_length > max_error >= 0 (scTagger.py:143)");
+    if (threads < 1) return fail(SCT_E_ARG, "threads must be >= 1");
+    int kpre = 0;
+    for (long long p = 1; threads > p; p *= 4) ++kpre;   // scTagger.py:689-697
+    if (kpre >= barcode_length - max_error)
+        return fail(SCT_E_ARG, "barcode_length - max_error must exceed the prefix length k=%d implied by -t %d "
+                    "(the reference leaks its -1 sentinel read id otherwise, SURVEY.md A.6)", kpre, threads);
+    if (barcode_length > DP_MAX_BL)
+        return fail(SCT_E_UNSUPPORTED, "barcode_length %d > %d is not implemented", barcode_length, DP_MAX_BL);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(SCT_E_CUDA, "no CUDA device available (sctagger_b200 has no CPU fallback)");
+    }
+    if (device < 0 || device >= ndev) return fail(SCT_E_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    CUDA_TRY(cudaSetDevice(device));
+    sct_handle *h = new (std::nothrow) sct_handle();
+    if (!h) return fail(SCT_E_NOMEM, "out of host memory");
+    h->device = device;
+    h->B = n_barcodes;
+    h->bl = barcode_length;
+    h->K = max_error;
+    h->threads = threads;
+    h->kpre = kpre;
+    h->mem_gb = mem_gb;
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    h->sm_count = prop.multiProcessorCount;
+    CUDA_TRY(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    h->use_dp = barcode_length > 16 || max_error > 3;
+
+    const int B = n_barcodes, bl = barcode_length;
+    const size_t W = ((size_t)B + 1) / 2;
+    h->n_tiles = (int)std::max<size_t>(1, (W + TILE_WORDS - 1) / TILE_WORDS);
+    std::vector<uint8_t> rcb((size_t)B * bl + 1), patF((size_t)B * bl + 1), patR((size_t)B * bl + 1);
+    for (int b = 0; b < B; ++b)
+        for (int i = 0; i < bl; ++i) {
+            const uint8_t c = barcodes[(size_t)b * bl + i];
+            if (!is_acgt(c)) h->clean_barcodes = false;
+            rcb[(size_t)b * bl + i] = comp_char(barcodes[(size_t)b * bl + (bl - 1 - i)]);
+        }
+    for (size_t i = 0; i < (size_t)B * bl; ++i) {
+        patF[i] = (uint8_t)map_char(barcodes[i]);
+        patR[i] = (uint8_t)map_char(rcb[i]);
+    }
+    CUDA_TRY(cudaMalloc(&h->d_patF, (size_t)B * bl + 1));
+    CUDA_TRY(cudaMalloc(&h->d_patR, (size_t)B * bl + 1));
+    CUDA_TRY(cudaMemcpy(h->d_patF, patF.data(), (size_t)B * bl + 1, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(h->d_patR, patR.data(), (size_t)B * bl + 1, cudaMemcpyHostToDevice));
+    if (!h->use_dp) {
+        // interleaved Eq tables, layout [tile][code][lane][4]; word w = tile*128 + lane*4 + q holds barcodes 2w, 2w+1
+        const size_t tab_words = (size_t)h->n_tiles * TILE_BYTES / 4;
+        std::vector<uint32_t> tF(tab_words, 0u), tR(tab_words, 0u);
+        for (int b = 0; b < B; ++b) {
+            const size_t w = (size_t)b >> 1;
+            const int f = b & 1;
+            const size_t tile = w / TILE_WORDS, lane = (w % TILE_WORDS) / 4, q = w % 4;
+            for (int i = 0; i < bl; ++i) {
+                const size_t baseF = tile * (TILE_BYTES / 4) + (size_t)patF[(size_t)b * bl + i] * 128 + lane * 4 + q;
+                const size_t baseR = tile * (TILE_BYTES / 4) + (size_t)patR[(size_t)b * bl + i] * 128 + lane * 4 + q;
+                tF[baseF] |= 1u << (2 * i + f);
+                tR[baseR] |= 1u << (2 * i + f);
+            }
+        }
+        CUDA_TRY(cudaMalloc(&h->d_tabF, tab_words * 4));
+        CUDA_TRY(cudaMalloc(&h->d_tabR, tab_words * 4));
+        CUDA_TRY(cudaMemcpy(h->d_tabF, tF.data(), tab_words * 4, cudaMemcpyHostToDevice));
+        CUDA_TRY(cudaMemcpy(h->d_tabR, tR.data(), tab_words * 4, cudaMemcpyHostToDevice));
+        h->fast_smem = (size_t)h->n_tiles * TILE_BYTES + (size_t)FAST_WARPS * FAST_LIST_CAP * 4 + 16;
+        h->fast_ok = h->clean_barcodes && h->fast_smem <= (size_t)h->max_smem_optin;
+        h->ovf_cap = h->n_tiles * 512;
+        CUDA_TRY(cudaMalloc(&h->d_ovf_scratch, (size_t)h->ovf_blocks * GEN_WARPS * h->ovf_cap * sizeof(uint32_t)));
+    }
+    // chunk sizing from -m: roughly 350 B of pinned + device memory per segment and two slots in flight
+    const double budget = mem_gb * (double)(1ull << 30);
+    int64_t segs = (int64_t)(budget / (2.0 * 350.0));
+    segs = std::min<int64_t>(std::max<int64_t>(segs, 1024), 1 << 21);
+    h->chunk_segs = segs;
+    h->chunk_bytes = segs * 40;
+    *out = h;
+    return SCT_OK;
+}
+
+int sct_destroy(sct_handle *h) {
+    if (!h) return SCT_OK;
+    cudaSetDevice(h->device);
+    for (Slot &s : h->slot) {
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        free_slot(s);
+        if (s.ev_start) cudaEventDestroy(s.ev_start);
+        if (s.ev_k0) cudaEventDestroy(s.ev_k0);
+        if (s.ev_k1) cudaEventDestroy(s.ev_k1);
+        if (s.ev_end) cudaEventDestroy(s.ev_end);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    dev_free(h->d_tabF); dev_free(h->d_tabR); dev_free(h->d_patF); dev_free(h->d_patR);
+    dev_free(h->d_ovf_scratch); dev_free(h->d_flush);
+    delete h;
+    return SCT_OK;
+}
+
+int sct_set_option(sct_handle *h, const char *key, int64_t value) {
+    if (!h || !key) return fail(SCT_E_ARG, "NULL argument");
+    const std::string k(key);
+    if (k == "chunk_segments") {
+        if (value < 1) return fail(SCT_E_ARG, "chunk_segments must be >= 1");
+        h->chunk_segs = value;
+        h->chunk_bytes = std::max<int64_t>(h->chunk_bytes, 64);
+    } else if (k == "chunk_bytes") {
+        if (value < 1) return fail(SCT_E_ARG, "chunk_bytes must be >= 1");
+        h->chunk_bytes = value;
+    } else if (k == "tie_capacity_per_segment") {
+        if (value < 0) return fail(SCT_E_ARG, "tie_capacity_per_segment must be >= 0");
+        h->tie_per_seg = (int)value;
+    } else if (k == "path") {   // 0 auto, 1 force the generic bit-parallel kernel, 2 force the DP kernel
+        if (value < 0 || value > 2) return fail(SCT_E_ARG, "path must be 0, 1 or 2");
+        if (value == 1 && h->use_dp) return fail(SCT_E_UNSUPPORTED, "bit-parallel kernels need barcode_length <= 16 and max_error <= 3");
+        h->path_override = (int)value;
+    } else {
+        return fail(SCT_E_ARG, "unknown option '%s'", key);
+    }
+    return SCT_OK;
+}
+
+int sct_stats(sct_handle *h, int64_t stats[8]) {
+    if (!h || !stats) return fail(SCT_E_ARG, "NULL argument");
+    memcpy(stats, h->stats, sizeof h->stats);
+    return SCT_OK;
+}
+
+int sct_chunk_capacity(sct_handle *h, int64_t *max_segments, int64_t *max_bytes) {
+    if (!h) return fail(SCT_E_ARG, "NULL handle");
+    if (max_segments) *max_segments = h->chunk_segs;
+    if (max_bytes) *max_bytes = h->chunk_bytes;
+    return SCT_OK;
+}
+
+int sct_match(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n, int32_t *min_ed,
+              int32_t *n_ties, int64_t *tie_offsets, const int32_t **tie_ids, int64_t *n_tie_ids) {
+    if (!h) return fail(SCT_E_ARG, "NULL handle");
+    if (n < 0) return fail(SCT_E_ARG, "n < 0");
+    if (!seg_offsets || !tie_offsets || !tie_ids || !n_tie_ids || (n > 0 && (!min_ed || !n_ties)))
+        return fail(SCT_E_ARG, "NULL argument");
+    if (n > 0 && !seg_bytes && seg_offsets[n] > seg_offsets[0]) return fail(SCT_E_ARG, "seg_bytes is NULL");
+    for (int64_t i = 0; i < n; ++i)
+        if (seg_offsets[i + 1] < seg_offsets[i]) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (at %lld)", (long long)i);
+    CUDA_TRY(cudaSetDevice(h->device));
+    memset(h->stats, 0, sizeof h->stats);
+    h->ties_host.clear();
+    h->staged = h->staged_ran = false;
+
+    int64_t tie_base = 0;
+    int64_t first = 0, chunk = 0;
+    int64_t pending[2] = {-1, -1};   // chunk index held by each slot
+    auto finish = [&](int si) -> int {
+        Slot &s = h->slot[si];
+        if (!s.busy) return SCT_OK;
+        TRY(complete_pass(h, s));
+        int64_t got = 0;
+        TRY(fetch_results(h, s, min_ed, n_ties, tie_offsets, s.first, tie_base, &got));
+        tie_base += got;
+        pending[si] = -1;
+        return SCT_OK;
+    };
+    while (first < n) {
+        int64_t cn = std::min<int64_t>(h->chunk_segs, n - first);
+        const int64_t limit = seg_offsets[first] + h->chunk_bytes;
+        if (seg_offsets[first + cn] > limit) {
+            const int64_t *e = std::upper_bound(seg_offsets + first, seg_offsets + first + cn + 1, limit);
+            cn = std::max<int64_t>(1, (e - (seg_offsets + first)) - 1);
+        }
+        const int si = (int)(chunk & 1);
+        TRY(finish(si));
+        TRY(start_chunk(h, h->slot[si], seg_bytes, seg_offsets, first, cn));
+        pending[si] = chunk;
+        first += cn;
+        ++chunk;
+    }
+    // drain in chunk order
+    const int a = (pending[0] >= 0 && (pending[1] < 0 || pending[0] < pending[1])) ? 0 : 1;
+    TRY(finish(a));
+    TRY(finish(1 - a));
+    tie_offsets[n] = tie_base;
+    *tie_ids = h->ties_host.empty() ? nullptr : h->ties_host.data();
+    *n_tie_ids = tie_base;
+    return SCT_OK;
+}
+
+int sct_stage(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n) {
+    if (!h || !seg_offsets || n < 0) return fail(SCT_E_ARG, "bad argument");
+    CUDA_TRY(cudaSetDevice(h->device));
+    Slot &s = h->slot[0];
+    const int64_t nbytes = seg_offsets[n] - seg_offsets[0];
+    if (n > h->chunk_segs || nbytes > h->chunk_bytes)
+        return fail(SCT_E_ARG, "batch of %lld segments / %lld bytes exceeds the chunk capacity %lld / %lld",
+                    (long long)n, (long long)nbytes, (long long)h->chunk_segs, (long long)h->chunk_bytes);
+    TRY(ensure_slot(h, s, n, nbytes));
+    const int64_t b0 = seg_offsets[0];
+    if (nbytes > 0) memcpy(s.h_bytes, seg_bytes + b0, (size_t)nbytes);
+    for (int64_t i = 0; i <= n; ++i) s.h_off[i] = seg_offsets[i] - b0;
+    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    s.n = n;
+    s.nbytes = nbytes;
+    s.first = 0;
+    h->staged = true;
+    h->staged_ran = false;
+    return SCT_OK;
+}
+
+int sct_run_staged(sct_handle *h, float *pass_ms, float *match_kernel_ms) {
+    if (!h) return fail(SCT_E_ARG, "NULL handle");
+    if (!h->staged) return fail(SCT_E_STATE, "sct_stage has not been called");
+    CUDA_TRY(cudaSetDevice(h->device));
+    Slot &s = h->slot[0];
+    memset(h->stats, 0, sizeof h->stats);
+    TRY(enqueue_pass(h, s, s.n));
+    TRY(complete_pass(h, s));
+    float a = 0.f, b = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&a, s.ev_start, s.ev_end));
+    CUDA_TRY(cudaEventElapsedTime(&b, s.ev_k0, s.ev_k1));
+    if (pass_ms) *pass_ms = a;
+    if (match_kernel_ms) *match_kernel_ms = b;
+    h->staged_ran = true;
+    return SCT_OK;
+}
+
+int sct_fetch_staged(sct_handle *h, int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets, const int32_t **tie_ids,
+                     int64_t *n_tie_ids) {
+    if (!h) return fail(SCT_E_ARG, "NULL handle");
+    if (!h->staged_ran) return fail(SCT_E_STATE, "sct_run_staged has not been called");
+    if (!tie_offsets || !tie_ids || !n_tie_ids) return fail(SCT_E_ARG, "NULL argument");
+    CUDA_TRY(cudaSetDevice(h->device));
+    Slot &s = h->slot[0];
+    h->ties_host.clear();
+    int64_t got = 0;
+    TRY(fetch_results(h, s, min_ed, n_ties, tie_offsets, 0, 0, &got));
+    tie_offsets[s.n] = got;
+    *tie_ids = h->ties_host.empty() ? nullptr : h->ties_host.data();
+    *n_tie_ids = got;
+    return SCT_OK;
+}
+
+int sct_flush_l2(sct_handle *h) {
+    if (!h) return fail(SCT_E_ARG, "NULL handle");
+    CUDA_TRY(cudaSetDevice(h->device));
+    if (!h->d_flush) CUDA_TRY(cudaMalloc(&h->d_flush, h->flush_bytes));
+    Slot &s = h->slot[0];
+    if (!s.stream) TRY(ensure_slot(h, s, 1, 1));
+    CUDA_TRY(cudaMemsetAsync(h->d_flush, 0x5a, h->flush_bytes, s.stream));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    return SCT_OK;
+}
+
+int sct_measure_int32_peak(int device, int mode, int repeats, double *lane_ops_per_s) {
+    if (!lane_ops_per_s || mode < 0 || mode > 2 || repeats < 1) return fail(SCT_E_ARG, "bad argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(SCT_E_CUDA, "no CUDA device available");
+    }
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    uint32_t *d_out = nullptr;
+    CUDA_TRY(cudaMalloc(&d_out, 64));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    const int blocks = prop.multiProcessorCount * 2, threads = 1024, iters = 4096;
+    double best = 0.0;
+    for (int r = 0; r < repeats + 1; ++r) {
+        CUDA_TRY(cudaEventRecord(e0));
+        if (mode == 0) int32_peak_kernel<0><<<blocks, threads>>>(d_out, iters, 12345u + r);
+        else if (mode == 1) int32_peak_kernel<1><<<blocks, threads>>>(d_out, iters, 12345u + r);
+        else int32_peak_kernel<2><<<blocks, threads>>>(d_out, iters, 12346u + 2 * r);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaEventRecord(e1));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        const double ops = (double)blocks * threads * (double)iters * 16.0 * 8.0;
+        if (r > 0) best = std::max(best, ops / (ms * 1e-3));   // r == 0 is the warm-up
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d_out);
+    *lane_ops_per_s = best;
+    return SCT_OK;
+}
+
+}  // extern "C"
