@@ -1,0 +1,263 @@
+"""ctypes binding of libsctagger_b200.so (C ABI: include/sctagger_b200.h).
+
+This is the only module that touches the shared library.  There is no CPU fallback: if the library
+is missing, or no CUDA device is visible, every compute entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libsctagger_b200.so")
+
+# every symbol include/sctagger_b200.h declares (checked by tests/test_abi.py)
+EXPORTS = (
+    "sct_device_count", "sct_last_error", "sct_create", "sct_destroy", "sct_match", "sct_stage",
+    "sct_run_staged", "sct_fetch_staged", "sct_stats", "sct_set_option", "sct_chunk_capacity",
+    "sct_measure_int32_peak", "sct_flush_l2",
+)
+
+_u8p = ctypes.POINTER(ctypes.c_uint8)
+_i32p = ctypes.POINTER(ctypes.c_int32)
+_i64p = ctypes.POINTER(ctypes.c_int64)
+_f32p = ctypes.POINTER(ctypes.c_float)
+_vp = ctypes.c_void_p
+
+_lib = None
+_lock = threading.Lock()
+
+
+class SctError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"sctagger_b200 error {code}: {msg}")
+        self.code = code
+
+
+def lib():
+    """Load the shared library (once).  Raises OSError with a build hint if it is missing."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(SO_PATH):
+                raise OSError(f"{SO_PATH} not found: build it with sctagger_b200/csrc/build.sh "
+                              f"(or __graft_entry__.build()); there is no CPU fallback")
+            L = ctypes.CDLL(SO_PATH)
+            L.sct_device_count.restype = ctypes.c_int
+            L.sct_device_count.argtypes = []
+            L.sct_last_error.restype = ctypes.c_char_p
+            L.sct_last_error.argtypes = []
+            L.sct_create.restype = ctypes.c_int
+            L.sct_create.argtypes = [ctypes.c_int, _u8p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                     ctypes.c_int32, ctypes.c_double, ctypes.POINTER(_vp)]
+            L.sct_destroy.restype = ctypes.c_int
+            L.sct_destroy.argtypes = [_vp]
+            L.sct_match.restype = ctypes.c_int
+            L.sct_match.argtypes = [_vp, _u8p, _i64p, ctypes.c_int64, _i32p, _i32p, _i64p,
+                                    ctypes.POINTER(_i32p), _i64p]
+            L.sct_stage.restype = ctypes.c_int
+            L.sct_stage.argtypes = [_vp, _u8p, _i64p, ctypes.c_int64]
+            L.sct_run_staged.restype = ctypes.c_int
+            L.sct_run_staged.argtypes = [_vp, _f32p, _f32p]
+            L.sct_fetch_staged.restype = ctypes.c_int
+            L.sct_fetch_staged.argtypes = [_vp, _i32p, _i32p, _i64p, ctypes.POINTER(_i32p), _i64p]
+            L.sct_stats.restype = ctypes.c_int
+            L.sct_stats.argtypes = [_vp, _i64p]
+            L.sct_set_option.restype = ctypes.c_int
+            L.sct_set_option.argtypes = [_vp, ctypes.c_char_p, ctypes.c_int64]
+            L.sct_chunk_capacity.restype = ctypes.c_int
+            L.sct_chunk_capacity.argtypes = [_vp, _i64p, _i64p]
+            L.sct_measure_int32_peak.restype = ctypes.c_int
+            L.sct_measure_int32_peak.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                 ctypes.POINTER(ctypes.c_double)]
+            L.sct_flush_l2.restype = ctypes.c_int
+            L.sct_flush_l2.argtypes = [_vp]
+            _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise SctError(rc, lib().sct_last_error().decode("utf-8", "replace"))
+
+
+def device_count() -> int:
+    return int(lib().sct_device_count())
+
+
+def _ptr(a, ct):
+    return a.ctypes.data_as(ctypes.POINTER(ct))
+
+
+def _as_u8(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a if a.size else np.zeros(1, dtype=np.uint8)
+
+
+STAT_NAMES = ("launches", "fast_segments", "generic_segments", "h2d_bytes", "d2h_bytes", "chunks",
+              "dp_segments", "reserved")
+
+
+class Matcher:
+    """One handle = one GPU with the barcode table resident (sct_create .. sct_destroy)."""
+
+    def __init__(self, barcodes: np.ndarray, max_error: int, threads: int = 16, mem_gb: float = 16.0,
+                 device: int = 0, **options):
+        barcodes = np.ascontiguousarray(barcodes, dtype=np.uint8)
+        if barcodes.ndim != 2:
+            raise ValueError("barcodes must be a (B, bl) uint8 matrix")
+        self._h = _vp()
+        self.n_barcodes, self.barcode_length = int(barcodes.shape[0]), int(barcodes.shape[1])
+        self.max_error = int(max_error)
+        self.device = int(device)
+        _check(lib().sct_create(int(device), _ptr(_as_u8(barcodes), ctypes.c_uint8), self.n_barcodes,
+                                self.barcode_length, int(max_error), int(threads), float(mem_gb),
+                                ctypes.byref(self._h)))
+        for k, v in options.items():
+            self.set_option(k, v)
+
+    def set_option(self, key: str, value: int):
+        _check(lib().sct_set_option(self._h, key.encode(), int(value)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().sct_destroy(self._h)
+            self._h = _vp()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- results ------------------------------------------------------------------------------------
+    @staticmethod
+    def _out(n):
+        return (np.empty(max(n, 1), dtype=np.int32), np.empty(max(n, 1), dtype=np.int32),
+                np.zeros(n + 1, dtype=np.int64))
+
+    @staticmethod
+    def _ties(ids, total):
+        if total == 0:
+            return np.zeros(0, dtype=np.int32)
+        return np.ctypeslib.as_array(ids, shape=(total,)).copy()
+
+    def match(self, seg_bytes: np.ndarray, offsets: np.ndarray):
+        """sct_match: host buffers in, host buffers out (chunked, pinned, double-buffered inside)."""
+        from .match_trie import MatchResult
+        sb = _as_u8(seg_bytes)
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        n = off.shape[0] - 1
+        min_ed, n_ties, tie_off = self._out(n)
+        ids = _i32p()
+        total = ctypes.c_int64(0)
+        _check(lib().sct_match(self._h, _ptr(sb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), n,
+                               _ptr(min_ed, ctypes.c_int32), _ptr(n_ties, ctypes.c_int32),
+                               _ptr(tie_off, ctypes.c_int64), ctypes.byref(ids), ctypes.byref(total)))
+        return MatchResult(min_ed[:n], n_ties[:n], tie_off, self._ties(ids, int(total.value)))
+
+    def stage(self, seg_bytes: np.ndarray, offsets: np.ndarray):
+        sb = _as_u8(seg_bytes)
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        self._staged_n = off.shape[0] - 1
+        _check(lib().sct_stage(self._h, _ptr(sb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), self._staged_n))
+
+    def run_staged(self):
+        """-> (pass_ms, match_kernel_ms): device time of one pass over the resident batch (CUDA events)."""
+        a, b = ctypes.c_float(0), ctypes.c_float(0)
+        _check(lib().sct_run_staged(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return float(a.value), float(b.value)
+
+    def fetch_staged(self):
+        from .match_trie import MatchResult
+        n = self._staged_n
+        min_ed, n_ties, tie_off = self._out(n)
+        ids = _i32p()
+        total = ctypes.c_int64(0)
+        _check(lib().sct_fetch_staged(self._h, _ptr(min_ed, ctypes.c_int32), _ptr(n_ties, ctypes.c_int32),
+                                      _ptr(tie_off, ctypes.c_int64), ctypes.byref(ids), ctypes.byref(total)))
+        return MatchResult(min_ed[:n], n_ties[:n], tie_off, self._ties(ids, int(total.value)))
+
+    def stats(self) -> dict:
+        s = np.zeros(8, dtype=np.int64)
+        _check(lib().sct_stats(self._h, _ptr(s, ctypes.c_int64)))
+        return dict(zip(STAT_NAMES, s.tolist()))
+
+    def chunk_capacity(self):
+        a, b = ctypes.c_int64(0), ctypes.c_int64(0)
+        _check(lib().sct_chunk_capacity(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return int(a.value), int(b.value)
+
+    def flush_l2(self):
+        _check(lib().sct_flush_l2(self._h))
+
+
+def measure_int32_peak(device: int = 0, mode: int = 0, repeats: int = 10) -> float:
+    v = ctypes.c_double(0)
+    _check(lib().sct_measure_int32_peak(device, mode, repeats, ctypes.byref(v)))
+    return float(v.value)
+
+
+def shard_bounds(n: int, parts: int):
+    """Contiguous read ranges, one per GPU: [(first, last), ...]."""
+    parts = max(1, parts)
+    return [((n * i) // parts, (n * (i + 1)) // parts) for i in range(parts)]
+
+
+def concat_results(parts):
+    """Concatenate per-shard MatchResults in read order (the host-side 'gather'; no collective)."""
+    from .match_trie import MatchResult
+    if len(parts) == 1:
+        return parts[0]
+    min_ed = np.concatenate([p.min_ed for p in parts])
+    n_ties = np.concatenate([p.n_ties for p in parts])
+    ids = np.concatenate([p.tie_ids for p in parts])
+    offs, base = [], 0
+    for p in parts:
+        offs.append(p.tie_offsets[:-1] + base)
+        base += int(p.tie_offsets[-1])
+    offs.append(np.array([base], dtype=np.int64))
+    return MatchResult(min_ed, n_ties, np.concatenate(offs), ids)
+
+
+def match_segments(barcodes: np.ndarray, seg_bytes: np.ndarray, offsets: np.ndarray, max_error: int,
+                   threads: int = 16, mem_gb: float = 16.0, devices=None, **options):
+    """All segments against all barcodes on one or several GPUs of this process.
+    devices: None = device 0; an int N = devices 0..N-1; or an explicit list.  Reads are split into
+    contiguous ranges, one host thread + one handle per GPU (ctypes releases the GIL), results are
+    concatenated in read order."""
+    if devices is None:
+        devices = [0]
+    elif isinstance(devices, int):
+        devices = list(range(devices))
+    devices = list(devices)
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    n = offsets.shape[0] - 1
+    if len(devices) == 1:
+        with Matcher(barcodes, max_error, threads, mem_gb, devices[0], **options) as m:
+            return m.match(seg_bytes, offsets)
+    bounds = shard_bounds(n, len(devices))
+    results = [None] * len(devices)
+    errors = []
+
+    def work(i):
+        try:
+            a, b = bounds[i]
+            with Matcher(barcodes, max_error, threads, mem_gb / len(devices), devices[i], **options) as m:
+                results[i] = m.match(seg_bytes, offsets[a:b + 1])
+        except Exception as e:  # re-raised in the caller
+            errors.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(len(devices))]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    if errors:
+        raise errors[0]
+    return concat_results(results)

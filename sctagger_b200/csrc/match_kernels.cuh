@@ -62,6 +62,7 @@ struct MatchParams {
     unsigned long long tie_cap;
     uint32_t *ovf_scratch;           // overflow re-run: per-warp tie lists in global memory
     int ovf_scratch_cap;             // entries per warp
+    uint32_t four;                   // always 4; a run-time value so that x*4+c stays an FMA-pipe IMAD (see shl2_add)
 };
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -97,19 +98,14 @@ __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void *src, uint
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
-// x*4 + addend as one integer multiply-add on the FMA pipe.  `four` is an opaque register holding 4 so that ptxas
-// cannot strength-reduce the multiply into an ALU-pipe shift/LEA: the ALU pipe is the bound of the recurrence.
+// x*4 + addend as one integer multiply-add on the FMA pipe (SASS: IMAD), leaving the ALU pipe to the LOP3s.  ptxas
+// constant-folds anything it can see (an `asm volatile("mov %0, 4")` included) and then strength-reduces x*4+c into an
+// ALU-pipe LEA, so the 4 has to arrive at run time: it is a kernel parameter (MatchParams::four, always 4).
 __device__ __forceinline__ uint32_t shl2_add(uint32_t x, uint32_t four, uint32_t addend) {
     uint32_t r;
     asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(four), "r"(addend));
     return r;
 }
-__device__ __forceinline__ uint32_t opaque_four() {
-    uint32_t f;
-    asm volatile("mov.u32 %0, 4;" : "=r"(f));
-    return f;
-}
-
 // One text column for one chain (one table word = two barcodes), clean segment: start state always active.
 template <int K>
 __device__ __forceinline__ void wm_step(uint32_t (&R)[K + 1], uint32_t (&S)[K + 1], uint32_t eq, uint32_t four) {
@@ -164,9 +160,8 @@ template <int K>
 __device__ __noinline__ unsigned long long tile_levels(const uint32_t *__restrict__ tabF_tile,
                                                        const uint32_t *__restrict__ tabR_tile,
                                                        const uint8_t *__restrict__ cols, int n, bool start0,
-                                                       uint32_t allv, int lane, int topshift) {
+                                                       uint32_t allv, int lane, int topshift, uint32_t four) {
     unsigned long long lv = 0;
-    const uint32_t four = opaque_four();
 #pragma unroll 1
     for (int strand = 0; strand < 2; ++strand) {
         const uint4 *tab = reinterpret_cast<const uint4 *>(strand ? tabF_tile : tabR_tile) + lane;
@@ -344,7 +339,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 1) match_fast_kernel(const Match
     mbar_wait(bar_a, 0);
 
     uint32_t *list = lists + warp * FAST_LIST_CAP;
-    const uint32_t four = opaque_four();
+    const uint32_t four = p.four;
     const int topshift = 2 * (p.bl - 1);
     const uint32_t topmask = 3u << topshift;
 
@@ -370,7 +365,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 1) match_fast_kernel(const Match
             }
             if (__any_sync(FULL, (h & topmask) != 0u)) {
                 const unsigned long long lv = tile_levels<K>(p.tabF + (size_t)t * (TILE_BYTES / 4), p.tabR + (size_t)t * (TILE_BYTES / 4),
-                                                             p.rec + (size_t)seg * REC_BYTES, n, true, 0xFu, lane, topshift);
+                                                             p.rec + (size_t)seg * REC_BYTES, n, true, 0xFu, lane, topshift, four);
                 fold_tile(lv, t, lane, K, best, count, list, FAST_LIST_CAP);
             }
         }
@@ -420,7 +415,7 @@ __global__ void __launch_bounds__(GEN_THREADS) match_generic_kernel(const MatchP
         int best = K + 1, count = 0;
         for (int t = 0; t < p.n_tiles; ++t) {
             const unsigned long long lv = tile_levels<K>(p.tabF + (size_t)t * (TILE_BYTES / 4), p.tabR + (size_t)t * (TILE_BYTES / 4),
-                                                         cols, n, start0, allv, lane, topshift);
+                                                         cols, n, start0, allv, lane, topshift, p.four);
             fold_tile(lv, t, lane, K, best, count, list, cap);
         }
         __syncwarp();
@@ -679,7 +674,8 @@ __global__ void __launch_bounds__(1024) scan_block_prefix(long long *__restrict_
 
 __global__ void __launch_bounds__(SCAN_BLOCK) scan_gather(const int *__restrict__ n_ties, int n, const long long *__restrict__ block_prefix,
                                                           const unsigned int *__restrict__ tie_start, const int *__restrict__ tie_buf,
-                                                          long long *__restrict__ tie_off, int *__restrict__ tie_out) {
+                                                          long long *__restrict__ tie_off, int *__restrict__ tie_out,
+                                                          unsigned long long tie_cap) {
     __shared__ long long warp_sums[32];
     const int i = blockIdx.x * SCAN_BLOCK + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -707,9 +703,11 @@ __global__ void __launch_bounds__(SCAN_BLOCK) scan_gather(const int *__restrict_
     if (i < n) {
         tie_off[i] = excl;
         if (i == n - 1) tie_off[n] = excl + c;
-        if (c > 0) {
+        // when the bump allocator ran past tie_cap the host grows the buffers and redoes the pass: write nothing here
+        if (c > 0 && (unsigned long long)(excl + c) <= tie_cap) {
             const unsigned int s = tie_start[i];
-            for (int k = 0; k < c; ++k) tie_out[excl + k] = tie_buf[s + k];
+            if ((unsigned long long)s + (unsigned long long)c <= tie_cap)
+                for (int k = 0; k < c; ++k) tie_out[excl + k] = tie_buf[s + k];
         }
     }
 }
@@ -719,11 +717,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) scan_gather(const int *__restrict_
 // inputs rotate so that consecutive logic ops cannot be algebraically merged.
 // ---------------------------------------------------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(1024) int32_peak_kernel(uint32_t *out, int iters, uint32_t seed) {
+__global__ void __launch_bounds__(1024) int32_peak_kernel(uint32_t *out, int iters, uint32_t seed, uint32_t four) {
     uint32_t a[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) a[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u + blockIdx.x;
-    const uint32_t four = opaque_four() + (seed & 1u);
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
         for (int r = 0; r < 16; ++r) {

@@ -216,6 +216,7 @@ MatchParams make_params(sct_handle *h, Slot &s) {
     p.tie_cap = s.tie_cap;
     p.ovf_scratch = h->d_ovf_scratch;
     p.ovf_scratch_cap = h->ovf_cap;
+    p.four = 4u;
     return p;
 }
 
@@ -281,7 +282,7 @@ int enqueue_pass(sct_handle *h, Slot &s, int64_t n) {
         CUDA_TRY(cudaGetLastError());
         scan_block_prefix<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total);
         CUDA_TRY(cudaGetLastError());
-        scan_gather<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums, s.d_tstart, s.d_tiebuf, s.d_toff, s.d_tieout);
+        scan_gather<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums, s.d_tstart, s.d_tiebuf, s.d_toff, s.d_tieout, s.tie_cap);
         CUDA_TRY(cudaGetLastError());
         launches += 3;
     } else {
@@ -652,9 +653,9 @@ int sct_measure_int32_peak(int device, int mode, int repeats, double *lane_ops_p
     double best = 0.0;
     for (int r = 0; r < repeats + 1; ++r) {
         CUDA_TRY(cudaEventRecord(e0));
-        if (mode == 0) int32_peak_kernel<0><<<blocks, threads>>>(d_out, iters, 12345u + r);
-        else if (mode == 1) int32_peak_kernel<1><<<blocks, threads>>>(d_out, iters, 12345u + r);
-        else int32_peak_kernel<2><<<blocks, threads>>>(d_out, iters, 12346u + 2 * r);
+        if (mode == 0) int32_peak_kernel<0><<<blocks, threads>>>(d_out, iters, 12345u + r, 4u);
+        else if (mode == 1) int32_peak_kernel<1><<<blocks, threads>>>(d_out, iters, 12345u + r, 4u);
+        else int32_peak_kernel<2><<<blocks, threads>>>(d_out, iters, 12346u + 2 * r, 4u);
         CUDA_TRY(cudaGetLastError());
         CUDA_TRY(cudaEventRecord(e1));
         CUDA_TRY(cudaEventSynchronize(e1));

@@ -1,0 +1,188 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (sctagger_b200._lib -> libsctagger_b200.so), against
+ (1) the UNMODIFIED reference's outputs committed under tests/golden/, byte for byte after formatting, and
+ (2) the CPU oracle on seeded random inputs, array for array (bit-exact: integer work).
+Edge cases follow SURVEY.md Appendix A.5: empty/short segments, non-ACGT bytes (t-dependent), palindromic and duplicated
+barcodes, barcodes with N, mr 0..3, bl 5..16, long segments, tie-list overflow, ragged chunking.
+"""
+import numpy as np
+import pytest
+
+import util
+from oracle import oracle
+from sctagger_b200 import _lib, synth
+from sctagger_b200 import match_trie as mt
+
+pytestmark = pytest.mark.gpu
+
+CASES = util.golden_cases()
+
+
+def _assert_same(got, want):
+    want = util.result_from_tuple(want) if isinstance(want, tuple) else want
+    assert np.array_equal(got.min_ed, want.min_ed)
+    assert np.array_equal(got.n_ties, want.n_ties)
+    assert np.array_equal(got.tie_offsets, want.tie_offsets)
+    assert np.array_equal(got.tie_ids, want.tie_ids)
+
+
+@pytest.mark.parametrize("c", CASES, ids=util.case_id)
+def test_golden_reference_outputs(c):
+    barcodes, reads, expected = util.load_case(c)
+    res = mt.run_get_matches_prefix(barcodes, reads, max_error=c["mr"], threads=c["t"], barcode_length=c["bl"])
+    got = mt.format_rows(reads.names, reads.seg_bytes, reads.offsets, res, barcodes)
+    assert got == expected
+
+
+@pytest.mark.parametrize("path", [1, 2], ids=["generic", "dp"])
+@pytest.mark.parametrize("c", [c for c in CASES if c["dir"] != "cfg1" and c["t"] in (1, 16)], ids=util.case_id)
+def test_golden_on_forced_paths(c, path):
+    barcodes, reads, expected = util.load_case(c)
+    bm = mt.barcode_matrix(barcodes, c["bl"])
+    res = _lib.match_segments(bm, reads.seg_bytes, reads.offsets, max_error=c["mr"], threads=c["t"], path=path)
+    assert mt.format_rows(reads.names, reads.seg_bytes, reads.offsets, res, barcodes) == expected
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_against_oracle(seed):
+    rng = np.random.default_rng(900 + seed)
+    bl = [16, 16, 16, 12, 8, 16, 15, 16, 10, 16, 5, 16][seed]
+    mr = [2, 3, 0, 1, 2, 1, 3, 2, 3, 2, 1, 3][seed]
+    t = [16, 1, 4, 17, 16, 5, 16, 64, 1, 16, 4, 16][seed]
+    dirty = [0.0, 0.3, 0.3, 0.2, 0.2, 0.0, 0.3, 0.5, 0.2, 0.0, 0.1, 0.0][seed]
+    n_bc = [700, 300, 513, 255, 256, 257, 1, 2, 1000, 2049, 64, 900][seed]
+    max_len = [40, 40, 40, 40, 40, 70, 40, 40, 40, 30, 20, 33][seed]
+    bc, sb, off = util.random_case(rng, n_bc, 1500, bl=bl, dirty=dirty, lower=True, max_len=max_len)
+    if seed in (3, 7, 8):   # barcodes holding non-ACGT bytes: scored as 'A' (scTagger.py:512-516)
+        bc = bc.copy()
+        bc[0, 2] = ord("N")
+        bc[-1, bl - 1] = ord("n")
+    want = oracle.match(bc, sb, off, mr, threads=t, algo="dp")
+    got = _lib.match_segments(bc, sb, off, max_error=mr, threads=t)
+    _assert_same(got, want)
+
+
+@pytest.mark.parametrize("bl,mr", [(17, 2), (24, 3), (32, 4), (16, 4), (16, 5)])
+def test_dp_kernel_ranges(bl, mr):
+    """barcode length 17..32 or max_error > 3 run on the DP kernel."""
+    rng = np.random.default_rng(bl * 10 + mr)
+    bc, sb, off = util.random_case(rng, 150, 600, bl=bl, dirty=0.1, max_len=bl + 20)
+    want = oracle.match(bc, sb, off, mr, threads=16, algo="dp")
+    got = _lib.match_segments(bc, sb, off, max_error=mr, threads=16)
+    _assert_same(got, want)
+
+
+def test_ragged_chunks_and_empty_inputs():
+    rng = np.random.default_rng(77)
+    bc, sb, off = util.random_case(rng, 300, 3000, bl=16, dirty=0.05)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, 2, threads=16, algo="dp"))
+    for chunk_segments, chunk_bytes in ((1, 1 << 20), (7, 1 << 20), (1000, 333), (4096, 1 << 20)):
+        with _lib.Matcher(bc, 2, 16, chunk_segments=chunk_segments, chunk_bytes=chunk_bytes) as m:
+            got = m.match(sb, off)
+            assert m.stats()["chunks"] >= min(3000, 3000 // chunk_segments)
+        _assert_same(got, want)
+    # n = 0 and all-empty segments
+    with _lib.Matcher(bc, 2, 16) as m:
+        r = m.match(np.zeros(0, np.uint8), np.zeros(1, np.int64))
+        assert r.min_ed.size == 0 and r.tie_offsets.tolist() == [0]
+        r = m.match(np.zeros(0, np.uint8), np.zeros(6, np.int64))
+        assert r.min_ed.tolist() == [-1] * 5 and r.n_ties.tolist() == [0] * 5 and r.tie_ids.size == 0
+
+
+def test_many_ties_overflow_rerun():
+    """Segments whose tie list is longer than the per-warp staging list (224) and than the device tie buffer."""
+    rng = np.random.default_rng(5)
+    one = np.frombuffer(b"ACGTTGCAAGGCTTAC", dtype=np.uint8)
+    bc = np.tile(one, (700, 1))                      # 700 copies of one barcode -> 700 forward ties
+    other = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=(100, 16))]
+    bc = np.concatenate([bc[:350], other, bc[350:]])
+    segs = [b"GG" + one.tobytes() + b"TTA", b"ACGTACGTACGTACGTACGTAA", one.tobytes()[:15] + b"CCCCC"] * 40
+    off = np.zeros(len(segs) + 1, np.int64)
+    np.cumsum([len(s) for s in segs], out=off[1:])
+    sb = np.frombuffer(b"".join(segs), np.uint8)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, 2, threads=16, algo="dp"))
+    assert want.n_ties.max() >= 700
+    got = _lib.match_segments(bc, sb, off, max_error=2, threads=16, tie_capacity_per_segment=1)
+    _assert_same(got, want)
+
+
+def test_cfg1_shape_vs_oracle_and_staged_api():
+    """BASELINE config 1 shape (10k x 1k, mr 2) through both entry points."""
+    bc = synth.make_barcodes(1000, 1001)
+    sb, off = synth.make_segments(bc, 10_000, 2001)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, 2, threads=16, algo="trie"))
+    with _lib.Matcher(bc, 2, 16) as m:
+        _assert_same(m.match(sb, off), want)
+        m.stage(sb, off)
+        pass_ms, kern_ms = m.run_staged()
+        assert pass_ms > 0 and 0 < kern_ms <= pass_ms
+        _assert_same(m.fetch_staged(), want)
+        st = m.stats()
+        assert st["launches"] >= 5 and st["fast_segments"] == 10_000
+
+
+def test_25k_barcodes_subsample_vs_oracle():
+    """BASELINE config 2 table size (25k barcodes: the full shared-memory table) on a sample the oracle finishes fast."""
+    bc = synth.make_barcodes(25_000, 1002)
+    sb, off = synth.make_segments(bc, 4000, 2002)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, 2, threads=16, algo="trie"))
+    got = _lib.match_segments(bc, sb, off, max_error=2, threads=16)
+    _assert_same(got, want)
+    want3 = util.result_from_tuple(oracle.match(bc, sb[:off[1500]], off[:1501], 3, threads=16, algo="trie"))
+    got3 = _lib.match_segments(bc, sb[:off[1500]], off[:1501], max_error=3, threads=16)
+    _assert_same(got3, want3)
+
+
+def test_full_size_properties():
+    """Config 2 size (1M x 25k would take ~seconds on the GPU; here 200k to stay quick): size-independent properties.
+    (a) sharding invariance: any split of the reads gives the concatenation of the parts;
+    (b) strand symmetry: reverse-complementing every segment swaps the strand bit of every tie and nothing else;
+    (c) planted exact barcodes are found at distance 0 with themselves among the ties."""
+    bc = synth.make_barcodes(25_000, 1002)
+    n = 200_000
+    sb, off = synth.make_segments(bc, n, 2003)
+    with _lib.Matcher(bc, 2, 16) as m:
+        full = m.match(sb, off)
+        parts = [m.match(sb, off[a:b + 1]) for a, b in _lib.shard_bounds(n, 3)]
+        _assert_same(_lib.concat_results(parts), full)
+        # (b)
+        comp = np.arange(256, dtype=np.uint8)
+        for x, y in (b"AT", b"CG", b"GC", b"TA"):
+            comp[x] = y
+        lens = np.diff(off)
+        rid = np.repeat(np.arange(n), lens)
+        pos = np.arange(sb.size) - off[rid]
+        src = off[rid] + (lens[rid] - 1 - pos)
+        rc = comp[sb[src]]
+        r = m.match(rc, off)
+        assert np.array_equal(r.min_ed, full.min_ed) and np.array_equal(r.n_ties, full.n_ties)
+        # tie ids with the strand bit flipped, re-sorted per read, must equal the original lists
+        flipped = r.tie_ids ^ 1
+        owner = np.repeat(np.arange(n), np.diff(r.tie_offsets))
+        order = np.lexsort((flipped, owner))
+        assert np.array_equal(flipped[order], full.tie_ids)
+    # (c)
+    rng = np.random.default_rng(9)
+    pick = rng.integers(0, 25_000, size=5000)
+    flank = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=(5000, 6))]
+    segs = np.concatenate([flank[:, :3], bc[pick], flank[:, 3:]], axis=1)
+    off2 = np.arange(5001, dtype=np.int64) * 22
+    r = _lib.match_segments(bc, segs.reshape(-1), off2, max_error=2, threads=16)
+    assert (r.min_ed == 0).all()
+    for i in range(0, 5000, 97):
+        assert ((int(pick[i]) << 1) | 1) in r.ties(i).tolist()
+
+
+def test_error_codes():
+    bc = synth.make_barcodes(10, 1)
+    with pytest.raises(_lib.SctError) as e:
+        _lib.Matcher(bc, 16, 16)            # bl > mr violated (scTagger.py:143)
+    assert e.value.code == -1
+    with pytest.raises(_lib.SctError):
+        _lib.Matcher(bc, 2, 16, mem_gb=0)   # mem > 0 (scTagger.py:141)
+    with pytest.raises(_lib.SctError):
+        _lib.Matcher(bc, 2, 16, device=99)
+    with _lib.Matcher(bc, 2, 16) as m:
+        with pytest.raises(_lib.SctError):
+            m.match(np.zeros(4, np.uint8), np.array([0, 3, 2], np.int64))   # decreasing offsets
+        with pytest.raises(_lib.SctError):
+            m.run_staged()                  # nothing staged
