@@ -3,7 +3,7 @@
 // error-bounded DFS per barcode; here every (segment, barcode, strand) triple is scored directly by a bit-parallel
 // automaton, one warp per segment, lanes over barcodes.  See DESIGN.md for the derivation and data layout.
 //
-// Arithmetic (checked bit-for-bit against the oracle by tests/wm_model.py, the numpy twin of this file):
+// Arithmetic (checked bit-for-bit on the CPU by tests/wm_model.py, the numpy twin of this file):
 //   k-error Shift-And automaton (Wu-Manber), one register R_d per error level, two 16-bit barcode fields interleaved
 //   per 32-bit word (barcode 2w = even bits, 2w+1 = odd bits) so a pattern shift is `x*4` and the always-active start
 //   state is `+3`:  S_d = 4*R_d + 3*v_d  — a single IMAD on the FMA pipe, leaving the ALU pipe to the LOP3s:
