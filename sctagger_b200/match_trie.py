@@ -173,8 +173,8 @@ def write_matches(outfile, data: bytes):
         sys.stdout.buffer.flush()
 
 
-def match_trie(args):
-    """Stage driver, same steps as reference scTagger.py:758-790."""
+def match_trie_bytes(args) -> bytes:
+    """Everything of reference scTagger.py:758-790 except opening the output file: -> the TSV rows."""
     barcodes = read_sr_barcodes(args.short_read_barcodes)
     barcode_lens = {len(b) for b in barcodes}
     assert barcode_lens == {args.barcode_length}, barcode_lens
@@ -182,5 +182,9 @@ def match_trie(args):
     result = run_get_matches_prefix(barcodes, reads, max_error=args.max_error, threads=args.threads,
                                     barcode_length=args.barcode_length, mem_gb=args.mem,
                                     devices=getattr(args, "devices", None))
-    write_matches(args.outfile, format_rows(reads.names, reads.seg_bytes, reads.offsets, result, barcodes))
-    return result
+    return format_rows(reads.names, reads.seg_bytes, reads.offsets, result, barcodes)
+
+
+def match_trie(args):
+    """Stage driver, same steps as reference scTagger.py:758-790."""
+    write_matches(args.outfile, match_trie_bytes(args))
