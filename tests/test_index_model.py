@@ -1,0 +1,39 @@
+"""CPU: the numpy/Python twin of the seeded kernel (pigeonhole seeds + role-swapped Shift-And verification) against
+the oracle, so that the arithmetic is proven before any GPU time is spent."""
+import numpy as np
+import pytest
+
+import index_model as im
+import util
+from oracle import oracle
+
+
+@pytest.mark.parametrize("bl,K,t", [(16, 2, 16), (16, 3, 1), (16, 1, 4), (16, 0, 16), (12, 2, 16), (10, 3, 1), (8, 1, 16), (15, 2, 5)])
+def test_model_equals_oracle(bl, K, t):
+    rng = np.random.default_rng(bl * 100 + K)
+    bc, sb, off = util.random_case(rng, 120, 400, bl=bl, dirty=0.0, max_len=31)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, K, threads=t, algo="dp"))
+    codes = np.vectorize(im.CODE.get)(bc).astype(np.uint8)
+    index = im.build_index(codes, K)
+    raw = sb.tobytes()
+    n_checked = 0
+    for r in range(len(off) - 1):
+        got = im.match_segment(codes, index, raw[off[r]:off[r + 1]], K)
+        if got is None:
+            continue
+        n_checked += 1
+        assert got[0] == want.min_ed[r], r
+        assert got[1] == want.ties(r).tolist(), r
+    assert n_checked > 300
+
+
+def test_piece_layout_is_disjoint_and_has_k_plus_1_pieces():
+    for bl in range(4, 17):
+        for K in range(0, min(4, bl)):
+            p = im.piece_layout(bl, K)
+            assert len(p) == K + 1
+            end = 0
+            for o, ln in p:
+                assert o >= end and 1 <= ln <= 8
+                end = o + ln
+            assert end <= bl
