@@ -88,14 +88,18 @@ int sct_fetch_staged(sct_handle *h, int32_t *min_ed, int32_t *n_ties, int64_t *t
 
 /* Counters of the last sct_match / sct_run_staged on this handle: [0] kernel launches, [1] segments on the
  * bit-parallel fast path, [2] segments on the generic path (non-ACGT bytes, > 32 bases, or tie-list overflow
- * re-runs), [3] host->device bytes, [4] device->host bytes, [5] chunks, [6] segments on the DP kernel, [7] reserved. */
+ * re-runs), [3] host->device bytes, [4] device->host bytes, [5] chunks, [6] segments on the DP kernel, [7] (barcode, strand)
+ * candidates the seeded kernel verified. */
 int sct_stats(sct_handle *h, int64_t stats[8]);
 
 /*
  * Tuning / test hooks (set before the first sct_match / sct_stage):
  *   "chunk_segments", "chunk_bytes"       override the chunk sizing derived from mem_gb
  *   "tie_capacity_per_segment"            initial size of the device tie buffer (it grows and the pass is redone if short)
- *   "path"                                0 = automatic, 1 = force the generic bit-parallel kernel, 2 = force the DP kernel
+ *   "path"                                0 = automatic (seeded kernel for clean segments of <= 31 bases), 1 = force the
+ *                                         generic bit-parallel kernel, 2 = force the DP kernel, 3 = use the all-pairs tile
+ *                                         kernel instead of the seeded one
+ *   "seed_ctas_per_sm"                    resident CTAs per SM of the seeded kernel (grid = SMs x this)
  */
 int sct_set_option(sct_handle *h, const char *key, int64_t value);
 

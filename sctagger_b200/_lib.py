@@ -98,7 +98,7 @@ def _as_u8(a):
 
 
 STAT_NAMES = ("launches", "fast_segments", "generic_segments", "h2d_bytes", "d2h_bytes", "chunks",
-              "dp_segments", "reserved")
+              "dp_segments", "seed_candidates")
 
 
 class Matcher:

@@ -40,7 +40,7 @@ struct Counters {                    // device-side cursors, zeroed before every
     unsigned int n_fast, n_gen, n_ovf, n_dp;
     unsigned int cur_fast, cur_gen, cur_ovf, cur_dp;
     unsigned long long tie_cursor;   // bump allocator over tie_buf (may run past tie_cap: the pass is then redone)
-    unsigned long long pad;
+    unsigned long long n_cand;       // seeded kernel: candidates verified (statistics)
 };
 
 struct MatchParams {
@@ -436,6 +436,8 @@ __device__ __forceinline__ int base_code(uint8_t b) {   // -1 for anything but u
 
 __global__ void __launch_bounds__(256) prep_kernel(const uint8_t *__restrict__ bytes, const long long *__restrict__ off,
                                                    int n_seg, int bl, int K, int kpre, int path /*0 auto,1 generic,2 dp*/,
+                                                   int fast_max /* longest segment of the fast path */,
+                                                   unsigned long long *__restrict__ pk /* 2-bit packed text, or NULL */,
                                                    uint8_t *__restrict__ rec, uint8_t *__restrict__ colinfo,
                                                    uint8_t *__restrict__ segflag, int *__restrict__ fast_list,
                                                    int *__restrict__ gen_list, int *__restrict__ dp_list,
@@ -457,7 +459,7 @@ __global__ void __launch_bounds__(256) prep_kernel(const uint8_t *__restrict__ b
         return;
     }
     bool clean = true;
-    if (L <= FAST_MAX_LEN && path == 0) {
+    if (L <= fast_max && path == 0) {
         uint32_t f[8] = {0, 0, 0, 0, 0, 0, 0, 0}, r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         const int n = (int)L;
 #pragma unroll
@@ -484,6 +486,12 @@ __global__ void __launch_bounds__(256) prep_kernel(const uint8_t *__restrict__ b
             dst[2] = make_uint4(r[0], r[1], r[2], r[3]);
             dst[3] = make_uint4(r[4], r[5], r[6], r[7]);
             segflag[i] = SEG_START0 | SEG_FAST;
+            if (pk) {
+                unsigned long long w = 0;
+#pragma unroll
+                for (int j = 0; j < FAST_MAX_LEN; ++j) w |= (unsigned long long)((f[j >> 2] >> (8 * (j & 3) + 1)) & 3u) << (2 * j);
+                pk[i] = w;
+            }
             fast_list[atomicAdd(&ctr->n_fast, 1u)] = i;
             return;
         }

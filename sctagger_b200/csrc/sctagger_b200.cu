@@ -4,6 +4,7 @@
 // stream per buffer) and every chunk is one pass of: prep -> match (fast / generic / overflow re-run | dp) -> finalize.
 // No PyTorch, no CPU fallback: every entry point fails with SCT_E_CUDA when there is no device.
 #include "match_kernels.cuh"
+#include "seed_kernels.cuh"
 #include "../../include/sctagger_b200.h"
 
 #include <algorithm>
@@ -76,6 +77,7 @@ struct Slot {
     uint8_t *d_bytes = nullptr, *d_colinfo = nullptr, *d_rec = nullptr, *d_segflag = nullptr;
     long long *d_off = nullptr;
     int *d_fast = nullptr, *d_gen = nullptr, *d_ovf = nullptr, *d_dp = nullptr;
+    unsigned long long *d_pk = nullptr;
     Counters *d_ctr = nullptr;
     int *d_min = nullptr, *d_nt = nullptr;
     unsigned int *d_tstart = nullptr;
@@ -99,11 +101,14 @@ struct sct_handle {
     uint32_t *d_tabF = nullptr, *d_tabR = nullptr;
     uint8_t *d_patF = nullptr, *d_patR = nullptr;
     int n_tiles = 0;
-    bool clean_barcodes = true, use_dp = false, fast_ok = false;
-    int path_override = 0;       // 0 auto, 1 force generic, 2 force dp
+    bool clean_barcodes = true, use_dp = false, fast_ok = false, seed_ok = false;
+    int path_override = 0;       // 0 auto, 1 force generic, 2 force dp, 3 force the tile (all-pairs) kernel
+    uint32_t *d_boff = nullptr, *d_ewords = nullptr, *d_eids = nullptr;
+    SeedIndex seed{};
     size_t fast_smem = 0;
     int64_t chunk_segs = 0, chunk_bytes = 0;
     int tie_per_seg = 8;
+    int seed_ctas_per_sm = 6;
     uint32_t *d_ovf_scratch = nullptr;
     int ovf_blocks = 16, ovf_cap = 0;
     uint8_t *d_flush = nullptr;
@@ -121,6 +126,7 @@ int free_slot(Slot &s) {
     host_free(s.h_ties); host_free(s.h_ctr); host_free(s.h_total);
     dev_free(s.d_bytes); dev_free(s.d_colinfo); dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off);
     dev_free(s.d_fast); dev_free(s.d_gen); dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_ctr);
+    dev_free(s.d_pk);
     dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart); dev_free(s.d_tiebuf); dev_free(s.d_tieout);
     dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_total);
     s.cap_segs = s.cap_bytes = 0;
@@ -157,7 +163,7 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
         dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off); dev_free(s.d_fast); dev_free(s.d_gen);
         dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart);
-        dev_free(s.d_toff); dev_free(s.d_bsums);
+        dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_pk);
         s.cap_segs = 0;
         CUDA_TRY(cudaMallocHost(&s.h_off, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMallocHost(&s.h_min, c * sizeof(int)));
@@ -165,6 +171,7 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         CUDA_TRY(cudaMallocHost(&s.h_toff, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_rec, (size_t)c * REC_BYTES));
         CUDA_TRY(cudaMalloc(&s.d_segflag, (size_t)c));
+        CUDA_TRY(cudaMalloc(&s.d_pk, (size_t)c * sizeof(unsigned long long)));
         CUDA_TRY(cudaMalloc(&s.d_off, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_fast, c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_gen, c * sizeof(int)));
@@ -221,8 +228,15 @@ MatchParams make_params(sct_handle *h, Slot &s) {
 }
 
 template <int K>
-int launch_match(sct_handle *h, Slot &s, const MatchParams &p, bool fast) {
-    if (fast) {
+int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 none, 1 tile kernel, 2 seeded kernel */) {
+    if (fast == 2) {
+        // seeded kernel: small static shared memory, many resident warps (latency-bound gathers + verification)
+        const int grid = h->sm_count * h->seed_ctas_per_sm;
+        if (h->bl == 16) match_seed_kernel<K, true><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
+        else match_seed_kernel<K, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
+    } else if (fast == 1) {
         if (h->bl == 16) {
             CUDA_TRY(cudaFuncSetAttribute(match_fast_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fast_smem));
             match_fast_kernel<K, true><<<h->sm_count, FAST_THREADS, h->fast_smem, s.stream>>>(p);
@@ -240,16 +254,25 @@ int launch_match(sct_handle *h, Slot &s, const MatchParams &p, bool fast) {
     return SCT_OK;
 }
 
+// Which kernel scores the clean short segments: 2 = seeded, 1 = tile (all pairs), 0 = none (generic / dp only).
+int fast_kind(const sct_handle *h) {
+    if (h->use_dp || h->path_override == 1 || h->path_override == 2) return 0;
+    if (h->path_override == 3) return h->fast_ok ? 1 : 0;
+    return h->seed_ok ? 2 : (h->fast_ok ? 1 : 0);
+}
+
 // Enqueue one full pass over the n segments resident in slot s (no host synchronisation).
 int enqueue_pass(sct_handle *h, Slot &s, int64_t n) {
-    const int path = h->path_override ? h->path_override : (h->use_dp ? 2 : (h->fast_ok ? 0 : 1));
+    const int fk = fast_kind(h);
+    const int path = h->use_dp || h->path_override == 2 ? 2 : (fk ? 0 : 1);
     MatchParams p = make_params(h, s);
     CUDA_TRY(cudaEventRecord(s.ev_start, s.stream));
     CUDA_TRY(cudaMemsetAsync(s.d_ctr, 0, sizeof(Counters), s.stream));
     int launches = 0;
     if (n > 0) {
         prep_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.d_bytes, s.d_off, (int)n, h->bl, h->K, h->kpre, path,
-                                                                     s.d_rec, s.d_colinfo, s.d_segflag, s.d_fast, s.d_gen,
+                                                                     fk == 2 ? SEED_MAX_LEN : FAST_MAX_LEN,
+                                                                     fk == 2 ? s.d_pk : nullptr, s.d_rec, s.d_colinfo, s.d_segflag, s.d_fast, s.d_gen,
                                                                      s.d_dp, s.d_ctr, s.d_min, s.d_nt);
         CUDA_TRY(cudaGetLastError());
         ++launches;
@@ -267,15 +290,14 @@ int enqueue_pass(sct_handle *h, Slot &s, int64_t n) {
             CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
             ++launches;
         } else {
-            const bool fast = path == 0;
             switch (h->K) {
-                case 0: TRY(launch_match<0>(h, s, p, fast)); break;
-                case 1: TRY(launch_match<1>(h, s, p, fast)); break;
-                case 2: TRY(launch_match<2>(h, s, p, fast)); break;
-                default: TRY(launch_match<3>(h, s, p, fast)); break;
+                case 0: TRY(launch_match<0>(h, s, p, fk)); break;
+                case 1: TRY(launch_match<1>(h, s, p, fk)); break;
+                case 2: TRY(launch_match<2>(h, s, p, fk)); break;
+                default: TRY(launch_match<3>(h, s, p, fk)); break;
             }
-            if (!fast) CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
-            launches += fast ? 3 : 2;
+            if (!fk) CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
+            launches += fk ? 3 : 2;
         }
         const int nb = (int)((n + SCAN_BLOCK - 1) / SCAN_BLOCK);
         scan_block_sums<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums);
@@ -305,6 +327,7 @@ int complete_pass(sct_handle *h, Slot &s) {
             h->stats[1] += s.h_ctr->n_fast;
             h->stats[2] += s.h_ctr->n_gen + s.h_ctr->n_ovf;
             h->stats[6] += s.h_ctr->n_dp;
+            h->stats[7] += (int64_t)s.h_ctr->n_cand;
             return SCT_OK;
         }
         const unsigned long long need = s.h_ctr->tie_cursor + 4096;
@@ -449,6 +472,58 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
         CUDA_TRY(cudaMemcpy(h->d_tabR, tR.data(), tab_words * 4, cudaMemcpyHostToDevice));
         h->fast_smem = (size_t)h->n_tiles * TILE_BYTES + (size_t)FAST_WARPS * FAST_LIST_CAP * 4 + 16;
         h->fast_ok = h->clean_barcodes && h->fast_smem <= (size_t)h->max_smem_optin;
+        // seeded kernel: K+1 disjoint pieces (longer pieces last, capped at 8 characters), one bucket table per piece
+        {
+            const int P = max_error + 1;
+            const int base = bl / P, extra = bl % P;
+            int o = 0, min_len = 99;
+            size_t boff_words = 0;
+            h->seed.n_pieces = P;
+            for (int q = 0; q < P && q < SEED_MAX_PIECES; ++q) {
+                const int ln = base + (q >= P - extra ? 1 : 0);
+                h->seed.piece_off[q] = o;
+                h->seed.piece_len[q] = std::min(ln, 8);
+                h->seed.boff_base[q] = (int)boff_words;
+                boff_words += ((size_t)1 << (2 * h->seed.piece_len[q])) + 1;
+                min_len = std::min(min_len, h->seed.piece_len[q]);
+                o += ln;
+            }
+            // below 4 characters per piece nearly every barcode is a candidate: the all-pairs tile kernel is faster there
+            h->seed_ok = h->clean_barcodes && P <= SEED_MAX_PIECES && min_len >= 4 && B > 0;
+            if (h->seed_ok) {
+                std::vector<uint32_t> boff(boff_words, 0u), ew((size_t)P * B), ei((size_t)P * B), code((size_t)B);
+                for (int b = 0; b < B; ++b) {
+                    uint32_t w = 0;
+                    for (int i = 0; i < bl; ++i) w |= (uint32_t)patF[(size_t)b * bl + i] << (2 * i);
+                    code[b] = w;
+                }
+                for (int q = 0; q < P; ++q) {
+                    const int po = h->seed.piece_off[q], ln = h->seed.piece_len[q];
+                    const uint32_t mask = (ln == 16) ? 0xFFFFFFFFu : ((1u << (2 * ln)) - 1u);
+                    uint32_t *bo = boff.data() + h->seed.boff_base[q];
+                    const size_t nb = (size_t)1 << (2 * ln);
+                    for (int b = 0; b < B; ++b) ++bo[((code[b] >> (2 * po)) & mask) + 1];
+                    bo[0] = (uint32_t)((size_t)q * B);
+                    for (size_t k = 1; k <= nb; ++k) bo[k] += bo[k - 1];
+                    std::vector<uint32_t> cur(bo, bo + nb);
+                    for (int b = 0; b < B; ++b) {            // ascending barcode id inside a bucket
+                        const uint32_t at = cur[(code[b] >> (2 * po)) & mask]++;
+                        ew[at] = code[b];
+                        ei[at] = (uint32_t)b;
+                    }
+                }
+                CUDA_TRY(cudaMalloc(&h->d_boff, boff.size() * 4));
+                CUDA_TRY(cudaMalloc(&h->d_ewords, ew.size() * 4));
+                CUDA_TRY(cudaMalloc(&h->d_eids, ei.size() * 4));
+                CUDA_TRY(cudaMemcpy(h->d_boff, boff.data(), boff.size() * 4, cudaMemcpyHostToDevice));
+                CUDA_TRY(cudaMemcpy(h->d_ewords, ew.data(), ew.size() * 4, cudaMemcpyHostToDevice));
+                CUDA_TRY(cudaMemcpy(h->d_eids, ei.data(), ei.size() * 4, cudaMemcpyHostToDevice));
+                h->seed.boff = h->d_boff;
+                h->seed.ewords = h->d_ewords;
+                h->seed.eids = h->d_eids;
+                h->seed.two = 2u;
+            }
+        }
         h->ovf_cap = h->n_tiles * 512;
         CUDA_TRY(cudaMalloc(&h->d_ovf_scratch, (size_t)h->ovf_blocks * GEN_WARPS * h->ovf_cap * sizeof(uint32_t)));
     }
@@ -476,6 +551,7 @@ int sct_destroy(sct_handle *h) {
     }
     dev_free(h->d_tabF); dev_free(h->d_tabR); dev_free(h->d_patF); dev_free(h->d_patR);
     dev_free(h->d_ovf_scratch); dev_free(h->d_flush);
+    dev_free(h->d_boff); dev_free(h->d_ewords); dev_free(h->d_eids);
     delete h;
     return SCT_OK;
 }
@@ -493,10 +569,16 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "tie_capacity_per_segment") {
         if (value < 0) return fail(SCT_E_ARG, "tie_capacity_per_segment must be >= 0");
         h->tie_per_seg = (int)value;
-    } else if (k == "path") {   // 0 auto, 1 force the generic bit-parallel kernel, 2 force the DP kernel
-        if (value < 0 || value > 2) return fail(SCT_E_ARG, "path must be 0, 1 or 2");
-        if (value == 1 && h->use_dp) return fail(SCT_E_UNSUPPORTED, "bit-parallel kernels need barcode_length <= 16 and max_error <= 3");
+    } else if (k == "path") {   // 0 auto, 1 generic bit-parallel kernel, 2 DP kernel, 3 tile (all-pairs) kernel instead of the seeded one
+        if (value < 0 || value > 3) return fail(SCT_E_ARG, "path must be 0..3");
+        if ((value == 1 || value == 3) && h->use_dp)
+            return fail(SCT_E_UNSUPPORTED, "bit-parallel kernels need barcode_length <= 16 and max_error <= 3");
+        if (value == 3 && !h->fast_ok)
+            return fail(SCT_E_UNSUPPORTED, "the tile kernel needs ACGT-only barcodes and a table that fits shared memory");
         h->path_override = (int)value;
+    } else if (k == "seed_ctas_per_sm") {
+        if (value < 1 || value > 32) return fail(SCT_E_ARG, "seed_ctas_per_sm must be 1..32");
+        h->seed_ctas_per_sm = (int)value;
     } else {
         return fail(SCT_E_ARG, "unknown option '%s'", key);
     }

@@ -1,0 +1,244 @@
+// SEEDED match kernel (sm_100a): pigeonhole seeds from a per-piece bucket index + exact bit-parallel verification.
+// Replaces, like match_fast_kernel, the reference's Trie.dfs / trie_search / merge (scTagger.py:566-599, 643-668,
+// 705-715) for clean ACGT segments of <= 31 bases, but scores only the (barcode, strand) pairs that can possibly be
+// within K edits instead of all 2B of them:
+//
+//   * The barcode is cut into K+1 disjoint pieces.  K edits destroy at most K pieces, so a barcode within K edits of a
+//     substring of the segment T has a piece occurring EXACTLY in T, at a text position j with
+//     o_p - K <= j <= n - (bl - o_p) + K.  Every piece has a bucket table (bucket = 2-bit code of the piece) built once
+//     in sct_create; a segment's candidates are therefore 2 strands x (K+1) pieces x <= 32 positions bucket ranges.
+//   * One warp owns one segment.  The ranges' lengths are prefix-summed (warp scan) into a per-warp slot table in shared
+//     memory; the flattened candidate list is then walked 32 candidates at a time, each lane finding its slot by binary
+//     search (load-balanced expansion: no lane idles on a short bucket).
+//   * Each candidate is scored exactly by a k-error Shift-And automaton with the roles swapped: the state vector runs
+//     over the positions of T (one 32-bit register), one barcode character is consumed per step, and Eq[c] — which
+//     positions of T hold character c — is warp-uniform per strand (8 words of shared memory per warp):
+//         R0' = (R0 << 1) & Eq[c]
+//         Rd' = ((Rd << 1) & Eq[c]) | R_{d-1} | (R_{d-1} << 1) | (R'_{d-1} << 1)         match | delete | subst | insert
+//     start R_d = all positions (free start in T); after bl steps the barcode is within d edits iff R_d & mask(n+1) != 0.
+//     The shifts are IMADs by a run-time 2 (FMA pipe), so the ALU pipe only sees the LOP3s and the character extract.
+//   * Reverse strand: d(revcomp(P), T) = d(P, revcomp(T)): revcomp(T) is scored against the same forward barcodes.
+//   * Hits (rare) are folded into the warp's (minimum, tie list); the list is sorted and de-duplicated at the end (a
+//     barcode is found once per surviving piece) so tie ids come out ascending = the reference's sorted((bid, strand)).
+// tests/index_model.py is the Python twin of this file.
+#pragma once
+#include "match_kernels.cuh"
+
+namespace sct {
+
+constexpr int SEED_THREADS = 256;
+constexpr int SEED_WARPS = SEED_THREADS / 32;
+constexpr int SEED_LIST_CAP = 96;          // hits staged per warp before sort + unique
+constexpr int SEED_MAX_LEN = 31;           // n + 1 state bits must fit one register
+constexpr int SEED_MAX_PIECES = 4;
+
+struct SeedIndex {
+    const uint32_t *boff;                  // per piece: 4^len + 1 absolute entry offsets, pieces concatenated
+    const uint32_t *ewords;                // entries: barcode as 2-bit codes, character i at bits 2i..2i+1
+    const uint32_t *eids;                  // entries: barcode index
+    int n_pieces;
+    int piece_off[SEED_MAX_PIECES];        // offset of the piece in the barcode
+    int piece_len[SEED_MAX_PIECES];
+    int boff_base[SEED_MAX_PIECES];        // start of the piece's bucket table inside boff
+    uint32_t two;                          // always 2 (run-time so that x*2 stays an FMA-pipe IMAD)
+};
+
+__device__ __forceinline__ uint32_t mul_rt(uint32_t x, uint32_t m) {
+    uint32_t r;
+    asm("mul.lo.u32 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(m));
+    return r;
+}
+
+// Exact level (0..K, or K+1) of one barcode word against the text whose Eq masks sit at shared address eq_a.
+template <int K, bool BL16>
+__device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t eq_a, uint32_t full, uint32_t two) {
+    uint32_t R[K + 1], S[K + 1];
+#pragma unroll
+    for (int d = 0; d <= K; ++d) {
+        R[d] = full;
+        S[d] = full << 1;
+    }
+    auto row = [&](uint32_t c4) {
+        uint32_t eq;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(eq) : "r"(eq_a + c4));
+        uint32_t r = S[0] & eq;
+        uint32_t s = mul_rt(r, two);
+        uint32_t pR = R[0], pS = S[0], nS = s;
+        R[0] = r;
+        S[0] = s;
+#pragma unroll
+        for (int d = 1; d <= K; ++d) {
+            const uint32_t t = pR | pS | nS;
+            r = (S[d] & eq) | t;
+            s = mul_rt(r, two);
+            pR = R[d];
+            pS = S[d];
+            nS = s;
+            R[d] = r;
+            S[d] = s;
+        }
+    };
+    if (BL16) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) row(i == 0 ? ((word << 2) & 0xCu) : ((word >> (2 * i - 2)) & 0xCu));
+    } else {
+        for (int i = 0; i < bl; ++i) row(((word >> (2 * i)) & 3u) << 2);
+    }
+    int level = K + 1;
+#pragma unroll
+    for (int d = K; d >= 0; --d)
+        if (R[d] & full) level = d;
+    return level;
+}
+
+// Sort the warp's hit list ascending and drop duplicates (rank sort through a second buffer).  Returns the new count.
+__device__ __forceinline__ int sort_unique(uint32_t *list, uint32_t *tmp, int count, int lane) {
+    if (count <= 1) return count;
+    for (int e = lane; e < count; e += 32) {
+        const uint32_t v = list[e];
+        int rank = 0;
+        for (int j = 0; j < count; ++j) {
+            const uint32_t u = list[j];
+            rank += (u < v) || (u == v && j < e);
+        }
+        tmp[rank] = v;
+    }
+    __syncwarp();
+    int out = 0;
+    for (int base = 0; base < count; base += 32) {
+        const int e = base + lane;
+        bool keep = false;
+        uint32_t v = 0;
+        if (e < count) {
+            v = tmp[e];
+            keep = e == 0 || tmp[e - 1] != v;
+        }
+        const unsigned m = __ballot_sync(FULL, keep);
+        if (keep) list[out + __popc(m & ((1u << lane) - 1u))] = v;
+        out += __popc(m);
+    }
+    __syncwarp();
+    return out;
+}
+
+template <int K, bool BL16>
+__global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchParams p, const SeedIndex ix,
+                                                                  const unsigned long long *__restrict__ pk) {
+    constexpr int NSLOT = 2 * (K + 1) * 32;
+    __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT];
+    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];
+    __shared__ __align__(16) uint32_t s_eq[SEED_WARPS][8];
+    __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
+    __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    uint32_t *prefix = s_prefix[warp], *start = s_start[warp], *list = s_list[warp], *tmp = s_tmp[warp];
+    const uint32_t eq_a = smem_u32(s_eq[warp]);
+    const unsigned int n_fast = p.ctr->n_fast;
+    const int bl = p.bl;
+    const int P = ix.n_pieces;
+    unsigned long long n_cand = 0;
+
+    for (;;) {
+        unsigned int idx = 0;
+        if (lane == 0) idx = atomicAdd(&p.ctr->cur_fast, 1u);
+        idx = __shfl_sync(FULL, idx, 0);
+        if (idx >= n_fast) break;
+        const int seg = p.fast_list[idx];
+        const int n = (int)(p.seg_off[seg + 1] - p.seg_off[seg]);
+        const unsigned long long fw = __ldg(pk + seg);
+        // reverse complement of the packed text: complement, reverse the 2-bit groups, drop the unused tail
+        unsigned long long rc = __brevll(~fw);
+        rc = ((rc & 0x5555555555555555ull) << 1) | ((rc >> 1) & 0x5555555555555555ull);
+        rc >>= (64 - 2 * n);
+        // Eq masks of both strands: bit j+1 of Eq[c] = [T[j] == c]
+        {
+            const uint32_t cj = (uint32_t)(fw >> (2 * lane)) & 3u;
+            const bool in = lane < n;
+            uint32_t bf[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) bf[c] = __ballot_sync(FULL, in && cj == (uint32_t)c);
+            if (lane < 4) {
+                const uint32_t f = lane == 0 ? bf[0] : lane == 1 ? bf[1] : lane == 2 ? bf[2] : bf[3];
+                const uint32_t g = lane == 0 ? bf[3] : lane == 1 ? bf[2] : lane == 2 ? bf[1] : bf[0];
+                s_eq[warp][4 + lane] = f << 1;                         // strand 1 = forward text
+                s_eq[warp][lane] = __brev(g) >> (31 - n);              // strand 0 = reverse-complemented text
+            }
+        }
+        // bucket ranges of every (strand, piece, position) slot, prefix-summed in slot order
+        uint32_t total = 0;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            const unsigned long long text = s ? fw : rc;               // slot groups: strand 0 first (ids sort that way)
+#pragma unroll
+            for (int q = 0; q <= K; ++q) {
+                uint32_t st = 0, len = 0;
+                if (q < P) {
+                    const int o = ix.piece_off[q], ln = ix.piece_len[q];
+                    const int lo = max(0, o - K), hi = min(n - ln, n - (bl - o) + K);
+                    if (lane >= lo && lane <= hi) {
+                        const uint32_t h = (uint32_t)(text >> (2 * lane)) & ((1u << (2 * ln)) - 1u);
+                        const uint32_t *b = ix.boff + ix.boff_base[q] + h;
+                        st = __ldg(b);
+                        len = __ldg(b + 1) - st;
+                    }
+                }
+                uint32_t incl = len;
+#pragma unroll
+                for (int o2 = 1; o2 < 32; o2 <<= 1) {
+                    const uint32_t v = __shfl_up_sync(FULL, incl, o2);
+                    if (lane >= o2) incl += v;
+                }
+                const int slot = (s * (K + 1) + q) * 32 + lane;
+                prefix[slot] = total + incl - len;
+                start[slot] = st;
+                total += __shfl_sync(FULL, incl, 31);
+            }
+        }
+        __syncwarp();
+        n_cand += total;
+        const uint32_t full = (n >= 31) ? 0xFFFFFFFFu : ((1u << (n + 1)) - 1u);
+        int best = K + 1, count = 0;
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            const uint32_t me = t0 + lane;
+            int level = K + 1;
+            uint32_t entry = 0, strand = 0;
+            if (me < total) {
+                int pos = 0;
+                constexpr int STEP0 = NSLOT > 128 ? 128 : NSLOT / 2;   // largest power of two below NSLOT
+#pragma unroll
+                for (int step = STEP0; step > 0; step >>= 1) {
+                    const int q = pos + step;
+                    if (q < NSLOT && prefix[q] <= me) pos = q;
+                }
+                entry = start[pos] + (me - prefix[pos]);
+                strand = pos >= (K + 1) * 32 ? 1u : 0u;
+                const uint32_t word = __ldg(ix.ewords + entry);
+                level = seed_verify<K, BL16>(word, bl, eq_a + strand * 16u, full, ix.two);
+            }
+            const unsigned hit = __ballot_sync(FULL, level <= K);
+            if (hit) {
+                const int m = __reduce_min_sync(FULL, level);
+                if (m <= best) {
+                    if (m < best) {
+                        best = m;
+                        count = 0;
+                    }
+                    const unsigned mine = __ballot_sync(FULL, level == m);
+                    if (level == m) {
+                        const int at = count + __popc(mine & ((1u << lane) - 1u));
+                        if (at < SEED_LIST_CAP) list[at] = (__ldg(ix.eids + entry) << 1) | strand;
+                    }
+                    count += __popc(mine);
+                }
+            }
+        }
+        __syncwarp();
+        if (count <= SEED_LIST_CAP) count = sort_unique(list, tmp, count, lane);
+        store_result(p, seg, lane, K, best, count, list, SEED_LIST_CAP, true);
+        __syncwarp();
+    }
+    if (lane == 0 && n_cand) atomicAdd(&p.ctr->n_cand, n_cand);
+}
+
+}  // namespace sct

@@ -33,11 +33,16 @@ def test_golden_reference_outputs(c):
     assert got == expected
 
 
-@pytest.mark.parametrize("path", [1, 2], ids=["generic", "dp"])
+@pytest.mark.parametrize("path", [1, 2, 3], ids=["generic", "dp", "tile"])
 @pytest.mark.parametrize("c", [c for c in CASES if c["dir"] != "cfg1" and c["t"] in (1, 16)], ids=util.case_id)
 def test_golden_on_forced_paths(c, path):
     barcodes, reads, expected = util.load_case(c)
     bm = mt.barcode_matrix(barcodes, c["bl"])
+    if path == 3 and not np.isin(bm, np.frombuffer(b"ACGT", np.uint8)).all():
+        with pytest.raises(_lib.SctError) as e:      # the tile kernel scores revcomp(T) against the forward table:
+            _lib.Matcher(bm, c["mr"], c["t"], path=3)  # only valid for ACGT-only barcodes (scTagger.py:148-156 keeps N)
+        assert e.value.code == -4
+        return
     res = _lib.match_segments(bm, reads.seg_bytes, reads.offsets, max_error=c["mr"], threads=c["t"], path=path)
     assert mt.format_rows(reads.names, reads.seg_bytes, reads.offsets, res, barcodes) == expected
 
@@ -59,6 +64,8 @@ def test_random_against_oracle(seed):
     want = oracle.match(bc, sb, off, mr, threads=t, algo="dp")
     got = _lib.match_segments(bc, sb, off, max_error=mr, threads=t)
     _assert_same(got, want)
+    if not (bc == ord("N")).any() and not (bc == ord("n")).any():
+        _assert_same(_lib.match_segments(bc, sb, off, max_error=mr, threads=t, path=3), want)   # all-pairs tile kernel
 
 
 @pytest.mark.parametrize("bl,mr", [(17, 2), (24, 3), (32, 4), (16, 4), (16, 5)])
