@@ -49,18 +49,25 @@ __device__ __forceinline__ uint32_t mul_rt(uint32_t x, uint32_t m) {
     return r;
 }
 
-// Exact level (0..K, or K+1) of one barcode word against the text whose Eq masks sit at shared address eq_a.
+// (a & b) | c in one LOP3
+__device__ __forceinline__ uint32_t and_or(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+
+// Exact level (0..K, or K+1) of one barcode word against one strand of the text.  tab_a is the shared-memory address
+// (128-byte aligned) of that strand's PAIR table: entry e = c0 | c1 << 2 holds {Eq[c0], Eq[c1]}, so one LDS.64 feeds
+// two steps of the automaton and the character extract is one shift + one LOP3 per two barcode characters.
 template <int K, bool BL16>
-__device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t eq_a, uint32_t full, uint32_t two) {
+__device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t tab_a, uint32_t full, uint32_t two) {
     uint32_t R[K + 1], S[K + 1];
 #pragma unroll
     for (int d = 0; d <= K; ++d) {
         R[d] = full;
         S[d] = full << 1;
     }
-    auto row = [&](uint32_t c4) {
-        uint32_t eq;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(eq) : "r"(eq_a + c4));
+    auto row = [&](uint32_t eq) {
         uint32_t r = S[0] & eq;
         uint32_t s = mul_rt(r, two);
         uint32_t pR = R[0], pS = S[0], nS = s;
@@ -80,9 +87,19 @@ __device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t eq_a,
     };
     if (BL16) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) row(i == 0 ? ((word << 2) & 0xCu) : ((word >> (2 * i - 2)) & 0xCu));
+        for (int m = 0; m < 8; ++m) {
+            const uint32_t sh = m == 0 ? (word << 3) : (word >> (4 * m - 3));
+            uint32_t e0, e1;
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(e0), "=r"(e1) : "r"(and_or(sh, 0x78u, tab_a)));
+            row(e0);
+            row(e1);
+        }
     } else {
-        for (int i = 0; i < bl; ++i) row(((word >> (2 * i)) & 3u) << 2);
+        for (int i = 0; i < bl; ++i) {
+            uint32_t e0;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e0) : "r"(tab_a + (((word >> (2 * i)) & 3u) << 3)));
+            row(e0);
+        }
     }
     int level = K + 1;
 #pragma unroll
@@ -125,18 +142,20 @@ template <int K, bool BL16>
 __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchParams p, const SeedIndex ix,
                                                                   const unsigned long long *__restrict__ pk) {
     constexpr int NSLOT = 2 * (K + 1) * 32;
-    __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT];
-    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];
-    __shared__ __align__(16) uint32_t s_eq[SEED_WARPS][8];
+    // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
+    __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
+    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket | strand << 31
+    __shared__ __align__(128) uint2 s_pair[SEED_WARPS][2][16]; // per strand: entry c0 | c1 << 2 = {Eq[c0], Eq[c1]}
     __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
     __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     uint32_t *prefix = s_prefix[warp], *start = s_start[warp], *list = s_list[warp], *tmp = s_tmp[warp];
-    const uint32_t eq_a = smem_u32(s_eq[warp]);
+    const uint32_t pair_a = smem_u32(&s_pair[warp][0][0]);
     const unsigned int n_fast = p.ctr->n_fast;
     const int bl = p.bl;
     const int P = ix.n_pieces;
+    const uint32_t lt_mask = (1u << lane) - 1u;
     unsigned long long n_cand = 0;
 
     for (;;) {
@@ -151,25 +170,27 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
         unsigned long long rc = __brevll(~fw);
         rc = ((rc & 0x5555555555555555ull) << 1) | ((rc >> 1) & 0x5555555555555555ull);
         rc >>= (64 - 2 * n);
-        // Eq masks of both strands: bit j+1 of Eq[c] = [T[j] == c]
+        // Eq masks (bit j+1 of Eq[c] = [T[j] == c]) of both strands, stored as pair tables: lane = strand * 16 + entry
         {
             const uint32_t cj = (uint32_t)(fw >> (2 * lane)) & 3u;
             const bool in = lane < n;
             uint32_t bf[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) bf[c] = __ballot_sync(FULL, in && cj == (uint32_t)c);
-            if (lane < 4) {
-                const uint32_t f = lane == 0 ? bf[0] : lane == 1 ? bf[1] : lane == 2 ? bf[2] : bf[3];
-                const uint32_t g = lane == 0 ? bf[3] : lane == 1 ? bf[2] : lane == 2 ? bf[1] : bf[0];
-                s_eq[warp][4 + lane] = f << 1;                         // strand 1 = forward text
-                s_eq[warp][lane] = __brev(g) >> (31 - n);              // strand 0 = reverse-complemented text
-            }
+            const bool fwd = lane >= 16;                                  // strand 1 = forward text
+            auto eq_of = [&](uint32_t c) -> uint32_t {
+                const uint32_t cc = fwd ? c : 3u - c;                     // reverse strand: complement ...
+                const uint32_t b = cc == 0 ? bf[0] : cc == 1 ? bf[1] : cc == 2 ? bf[2] : bf[3];
+                return fwd ? (b << 1) : (__brev(b) >> (31 - n));          // ... and reversed positions
+            };
+            s_pair[warp][lane >> 4][lane & 15] = make_uint2(eq_of(lane & 3u), eq_of((lane >> 2) & 3u));
         }
-        // bucket ranges of every (strand, piece, position) slot, prefix-summed in slot order
+        // bucket ranges of every (strand, piece, position); the non-empty ones become slots, prefix-summed in order
         uint32_t total = 0;
+        int n_slots = 0;
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-            const unsigned long long text = s ? fw : rc;               // slot groups: strand 0 first (ids sort that way)
+            const unsigned long long text = s ? fw : rc;               // strand 0 first
 #pragma unroll
             for (int q = 0; q <= K; ++q) {
                 uint32_t st = 0, len = 0;
@@ -189,32 +210,37 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
                     const uint32_t v = __shfl_up_sync(FULL, incl, o2);
                     if (lane >= o2) incl += v;
                 }
-                const int slot = (s * (K + 1) + q) * 32 + lane;
-                prefix[slot] = total + incl - len;
-                start[slot] = st;
+                const unsigned live = __ballot_sync(FULL, len != 0u);
+                if (len) {
+                    const int slot = n_slots + __popc(live & lt_mask);
+                    prefix[slot] = total + incl - len;
+                    start[slot] = st | ((uint32_t)s << 31);
+                }
+                n_slots += __popc(live);
                 total += __shfl_sync(FULL, incl, 31);
             }
         }
+        prefix[n_slots + lane] = 0xFFFFFFFFu;
         __syncwarp();
         n_cand += total;
         const uint32_t full = (n >= 31) ? 0xFFFFFFFFu : ((1u << (n + 1)) - 1u);
         int best = K + 1, count = 0;
+        int cur = 0;                                                    // slot holding candidate t0 (warp-uniform)
         for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            // slots starting at t0 + r, 1 <= r <= 32, as bit r-1: a lane's slot is cur + #starts at or before it
+            const uint32_t rel = prefix[cur + 1 + lane] - t0 - 1u;
+            const uint32_t heads = __reduce_or_sync(FULL, rel < 32u ? (1u << rel) : 0u);
+            const int pos = cur + __popc(heads & lt_mask);
+            cur += __popc(heads);
             const uint32_t me = t0 + lane;
             int level = K + 1;
             uint32_t entry = 0, strand = 0;
             if (me < total) {
-                int pos = 0;
-                constexpr int STEP0 = NSLOT > 128 ? 128 : NSLOT / 2;   // largest power of two below NSLOT
-#pragma unroll
-                for (int step = STEP0; step > 0; step >>= 1) {
-                    const int q = pos + step;
-                    if (q < NSLOT && prefix[q] <= me) pos = q;
-                }
-                entry = start[pos] + (me - prefix[pos]);
-                strand = pos >= (K + 1) * 32 ? 1u : 0u;
+                const uint32_t sw = start[pos];
+                strand = sw >> 31;
+                entry = (sw & 0x7FFFFFFFu) + (me - prefix[pos]);
                 const uint32_t word = __ldg(ix.ewords + entry);
-                level = seed_verify<K, BL16>(word, bl, eq_a + strand * 16u, full, ix.two);
+                level = seed_verify<K, BL16>(word, bl, pair_a + strand * 128u, full, ix.two);
             }
             const unsigned hit = __ballot_sync(FULL, level <= K);
             if (hit) {
@@ -226,7 +252,7 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
                     }
                     const unsigned mine = __ballot_sync(FULL, level == m);
                     if (level == m) {
-                        const int at = count + __popc(mine & ((1u << lane) - 1u));
+                        const int at = count + __popc(mine & lt_mask);
                         if (at < SEED_LIST_CAP) list[at] = (__ldg(ix.eids + entry) << 1) | strand;
                     }
                     count += __popc(mine);
