@@ -251,6 +251,20 @@ def main():
     kern_s = kern_ms * 1e-3 / a.steps
     achieved = work / kern_s
     all_rows = sum_over_ranks(rows)
+    seeded = stats["seed_candidates"] > 0
+    kernel_name = (f"match_seed_kernel<{a.max_error},true>" if seeded else f"match_fast_kernel<{a.max_error},true>")
+    prof = _ncu_profile(f"r01_ncu_match_seed_K{a.max_error}.txt") if seeded else {}
+    executed = None
+    if seeded and prof.get("alu_pct") and prof.get("ms"):
+        # ALU-pipe lane-ops the kernel actually issues, per verified candidate, from the committed ncu capture
+        # (pipe utilisation x measured LOP3 peak x kernel time / candidates); scaled by this run's candidates and time.
+        cand = stats["seed_candidates"]
+        per_cand = prof["alu_pct"] / 100.0 * 18.5e12 * prof["ms"] * 1e-3 / (prof.get("cand_per_launch") or cand)
+        executed = {"candidates_per_segment": cand / n, "alu_lane_ops_per_candidate": per_cand,
+                    "alu_T_lane_ops_per_s": cand * per_cand / kern_s / 1e12,
+                    "frac_of_peak": cand * per_cand / kern_s / peak_lop3,
+                    "ncu_alu_pipe_pct": prof["alu_pct"], "ncu_issue_ipc": prof.get("ipc"),
+                    "source": f"profiles/r01_ncu_match_seed_K{a.max_error}.txt"}
     m.close()
 
     if rank == 0:
@@ -267,9 +281,14 @@ def main():
                     "api": "sctagger_b200._lib.Matcher.match -> sct_match (host numpy in/out)"},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"bound": "int32_alu", "kernel": "match_fast_kernel<2,true>",
+            "roofline": {"bound": "int32_alu", "kernel": kernel_name,
                          "achieved": achieved / 1e12, "peak": peak_lop3 / 1e12, "unit": "T lane-op/s",
-                         "frac": achieved / peak_lop3, "traffic": None,
+                         "frac": achieved / peak_lop3, "traffic": prof.get("dram_bytes"),
+                         "note": "achieved = ALGORITHMIC lane-ops (14 per Myers column update x 2B x sum(len), no credit "
+                                 "taken for skipped work) / kernel time; the seeded kernel verifies only the pigeonhole "
+                                 "candidates, so frac reads far above 1 - kernel quality is `executed` (ALU-pipe "
+                                 "utilisation of the instructions actually issued)",
+                         "executed": executed,
                          "peak_source": "measured live: sct_measure_int32_peak (independent LOP3 chains, all SMs)",
                          "peak_lop3_plus_imad": peak_mix / 1e12,
                          "algorithmic_ops_per_launch": work, "kernel_ms": kern_ms / a.steps,
@@ -289,6 +308,41 @@ def main():
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def _ncu_profile(name):
+    """Numbers of the committed ncu capture of the dominant kernel (profiles/<name>), launch 0."""
+    out = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            lines = f.read().split("--- launch ID 1")[0].splitlines()
+    except OSError:
+        return out
+    rd = wr = None
+    for ln in lines:
+        c = ln.split()
+        if not c:
+            continue
+        try:
+            v = float(c[-1].replace(",", ""))
+        except ValueError:
+            continue
+        scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(c[1] if len(c) > 2 else "", 1.0)
+        if c[0] == "gpu__time_duration.sum":
+            out["ms"] = v
+        elif c[0] == "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active":
+            out["alu_pct"] = v
+        elif c[0] == "smsp__issue_active.avg.per_cycle_active":
+            out["ipc"] = v
+        elif c[0] == "dram__bytes_read.sum":
+            rd = v * scale
+        elif c[0] == "dram__bytes_write.sum":
+            wr = v * scale
+        elif c[0] == "#" and "candidates_per_launch" in ln:
+            out["cand_per_launch"] = v
+    if rd is not None and wr is not None:
+        out["dram_bytes"] = rd + wr
+    return out
 
 
 def _peaks():

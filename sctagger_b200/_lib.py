@@ -139,7 +139,7 @@ class Matcher:
     @staticmethod
     def _out(n):
         return (np.empty(max(n, 1), dtype=np.int32), np.empty(max(n, 1), dtype=np.int32),
-                np.zeros(n + 1, dtype=np.int64))
+                np.empty(n + 1, dtype=np.int64))
 
     @staticmethod
     def _ties(ids, total):

@@ -8,12 +8,15 @@
 #include "../../include/sctagger_b200.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
+#include <omp.h>
 #include <vector>
 
 using namespace sct;
@@ -21,6 +24,16 @@ using namespace sct;
 namespace {
 
 thread_local std::string g_err;
+
+// SCT_TRACE=1: per-call host-side phase times of sct_match on stderr (staging / waiting on the GPU / un-staging)
+struct Trace {
+    bool on = getenv("SCT_TRACE") != nullptr;
+    double t_stage = 0, t_wait = 0, t_fetch = 0, t_check = 0;
+    static double now() {
+        return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+    }
+};
+thread_local Trace g_tr;
 
 int fail(int code, const char *fmt, ...) {
     char buf[1024];
@@ -50,6 +63,20 @@ inline uint8_t comp_char(uint8_t c) {                                           
     return c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : c;
 }
 inline bool is_acgt(uint8_t c) { return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }
+
+// memcpy split over the handle's host worker threads (-t): staging and un-staging are the host-serial part of sct_match
+void par_memcpy(void *dst, const void *src, size_t bytes, int nt) {
+    if (nt <= 1 || bytes < (1u << 20)) {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    const size_t piece = ((bytes + nt - 1) / nt + 63) & ~(size_t)63;
+#pragma omp parallel for num_threads(nt) schedule(static)
+    for (int t = 0; t < nt; ++t) {
+        const size_t a = std::min(bytes, piece * t), b = std::min(bytes, piece * (t + 1));
+        if (b > a) memcpy((char *)dst + a, (const char *)src + a, b - a);
+    }
+}
 
 template <class T>
 void dev_free(T *&p) {
@@ -88,6 +115,7 @@ struct Slot {
     // in flight
     int64_t n = 0, nbytes = 0, first = 0;
     bool busy = false;
+    bool copies_enqueued = false;   // the fixed-size result copies follow the pass on the stream (sct_match)
 };
 
 }  // namespace
@@ -106,7 +134,9 @@ struct sct_handle {
     uint32_t *d_boff = nullptr, *d_ewords = nullptr, *d_eids = nullptr;
     SeedIndex seed{};
     size_t fast_smem = 0;
-    int64_t chunk_segs = 0, chunk_bytes = 0;
+    int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
+    int64_t stream_segs = 0;                    // segments per streamed chunk of sct_match (<= chunk_segs)
+    int host_threads = 1;        // worker threads for staging / un-staging (from -t, capped)
     int tie_per_seg = 8;
     int seed_ctas_per_sm = 6;
     uint32_t *d_ovf_scratch = nullptr;
@@ -319,10 +349,22 @@ int enqueue_pass(sct_handle *h, Slot &s, int64_t n) {
     return SCT_OK;
 }
 
+// Fixed-size results (min_ed, n_ties, tie offsets) start their way back right behind the kernels of the pass.
+int enqueue_result_copies(Slot &s) {
+    const int64_t n = s.n;
+    if (n <= 0) return SCT_OK;
+    CUDA_TRY(cudaMemcpyAsync(s.h_min, s.d_min, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_nt, s.d_nt, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_toff, s.d_toff, (size_t)(n + 1) * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    return SCT_OK;
+}
+
 // Wait for the pass in slot s; if the bump-allocated tie buffer was too small, grow it and redo the pass.
 int complete_pass(sct_handle *h, Slot &s) {
     for (int attempt = 0; attempt < 4; ++attempt) {
+        const double t0 = Trace::now();
         CUDA_TRY(cudaStreamSynchronize(s.stream));
+        g_tr.t_wait += Trace::now() - t0;
         if (s.h_ctr->tie_cursor <= s.tie_cap) {
             h->stats[1] += s.h_ctr->n_fast;
             h->stats[2] += s.h_ctr->n_gen + s.h_ctr->n_ovf;
@@ -333,6 +375,7 @@ int complete_pass(sct_handle *h, Slot &s) {
         const unsigned long long need = s.h_ctr->tie_cursor + 4096;
         TRY(alloc_ties(s, need));
         TRY(enqueue_pass(h, s, s.n));
+        if (s.copies_enqueued) TRY(enqueue_result_copies(s));
     }
     return fail(SCT_E_STATE, "tie buffer did not converge");
 }
@@ -340,9 +383,22 @@ int complete_pass(sct_handle *h, Slot &s) {
 // Copy chunk [first, first+n) of the caller's arrays into the slot's pinned staging and start H2D + pass.
 int start_chunk(sct_handle *h, Slot &s, const uint8_t *seg_bytes, const int64_t *off, int64_t first, int64_t n) {
     const int64_t b0 = off[first], nbytes = off[first + n] - b0;
+    if (nbytes < 0) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
     TRY(ensure_slot(h, s, n, nbytes));
-    if (nbytes > 0) memcpy(s.h_bytes, seg_bytes + b0, (size_t)nbytes);
-    for (int64_t i = 0; i <= n; ++i) s.h_off[i] = off[first + i] - b0;
+    const double t0 = Trace::now();
+    if (nbytes > 0) par_memcpy(s.h_bytes, seg_bytes + b0, (size_t)nbytes, h->host_threads);
+    {
+        long long *dst = s.h_off;
+        const int64_t *src = off + first;
+        bool bad = false;
+#pragma omp parallel for num_threads(h->host_threads) schedule(static) reduction(|| : bad) if (n > (1 << 16))
+        for (int64_t i = 0; i <= n; ++i) {
+            dst[i] = src[i] - b0;
+            if (i < n && src[i + 1] < src[i]) bad = true;
+        }
+        if (bad) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
+    }
+    g_tr.t_stage += Trace::now() - t0;
     s.n = n;
     s.nbytes = nbytes;
     s.first = first;
@@ -351,6 +407,8 @@ int start_chunk(sct_handle *h, Slot &s, const uint8_t *seg_bytes, const int64_t 
     h->stats[3] += nbytes + (n + 1) * (int64_t)sizeof(long long);
     h->stats[5] += 1;
     TRY(enqueue_pass(h, s, n));
+    TRY(enqueue_result_copies(s));
+    s.copies_enqueued = true;
     s.busy = true;
     return SCT_OK;
 }
@@ -361,20 +419,32 @@ int fetch_results(sct_handle *h, Slot &s, int32_t *min_ed, int32_t *n_ties, int6
     const int64_t n = s.n;
     const long long total = n > 0 ? *s.h_total : 0;
     if (n > 0) {
-        CUDA_TRY(cudaMemcpyAsync(s.h_min, s.d_min, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-        CUDA_TRY(cudaMemcpyAsync(s.h_nt, s.d_nt, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-        CUDA_TRY(cudaMemcpyAsync(s.h_toff, s.d_toff, (size_t)(n + 1) * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+        if (!s.copies_enqueued) TRY(enqueue_result_copies(s));
         if (total > 0)
             CUDA_TRY(cudaMemcpyAsync(s.h_ties, s.d_tieout, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        double t0 = Trace::now();
         CUDA_TRY(cudaStreamSynchronize(s.stream));
+        g_tr.t_wait += Trace::now() - t0;
+        t0 = Trace::now();
         h->stats[4] += n * 8 + (n + 1) * 8 + total * 4;
-        memcpy(min_ed + out_first, s.h_min, (size_t)n * sizeof(int));
-        memcpy(n_ties + out_first, s.h_nt, (size_t)n * sizeof(int));
-        for (int64_t i = 0; i < n; ++i) tie_offsets[out_first + i] = tie_base + s.h_toff[i];
-        if (total > 0) h->ties_host.insert(h->ties_host.end(), s.h_ties, s.h_ties + total);
+        par_memcpy(min_ed + out_first, s.h_min, (size_t)n * sizeof(int), h->host_threads);
+        par_memcpy(n_ties + out_first, s.h_nt, (size_t)n * sizeof(int), h->host_threads);
+        {
+            int64_t *dst = tie_offsets + out_first;
+            const long long *src = s.h_toff;
+#pragma omp parallel for num_threads(h->host_threads) schedule(static) if (n > (1 << 16))
+            for (int64_t i = 0; i < n; ++i) dst[i] = tie_base + src[i];
+        }
+        if (total > 0) {
+            const size_t at = h->ties_host.size();
+            h->ties_host.resize(at + (size_t)total);
+            par_memcpy(h->ties_host.data() + at, s.h_ties, (size_t)total * sizeof(int), h->host_threads);
+        }
+        g_tr.t_fetch += Trace::now() - t0;
     }
     *n_new_ties = total;
     s.busy = false;
+    s.copies_enqueued = false;
     return SCT_OK;
 }
 
@@ -427,6 +497,7 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
     h->threads = threads;
     h->kpre = kpre;
     h->mem_gb = mem_gb;
+    h->host_threads = std::max(1, std::min({(int)threads, 8, (int)std::thread::hardware_concurrency()}));
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
@@ -533,6 +604,8 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
     segs = std::min<int64_t>(std::max<int64_t>(segs, 1024), 1 << 21);
     h->chunk_segs = segs;
     h->chunk_bytes = segs * 40;
+    // streamed chunks are kept small enough that staging / copies of one chunk overlap the kernels of the other slot
+    h->stream_segs = std::min<int64_t>(segs, 1 << 18);
     *out = h;
     return SCT_OK;
 }
@@ -562,6 +635,7 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     if (k == "chunk_segments") {
         if (value < 1) return fail(SCT_E_ARG, "chunk_segments must be >= 1");
         h->chunk_segs = value;
+        h->stream_segs = value;
         h->chunk_bytes = std::max<int64_t>(h->chunk_bytes, 64);
     } else if (k == "chunk_bytes") {
         if (value < 1) return fail(SCT_E_ARG, "chunk_bytes must be >= 1");
@@ -605,8 +679,9 @@ int sct_match(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offset
     if (!seg_offsets || !tie_offsets || !tie_ids || !n_tie_ids || (n > 0 && (!min_ed || !n_ties)))
         return fail(SCT_E_ARG, "NULL argument");
     if (n > 0 && !seg_bytes && seg_offsets[n] > seg_offsets[0]) return fail(SCT_E_ARG, "seg_bytes is NULL");
-    for (int64_t i = 0; i < n; ++i)
-        if (seg_offsets[i + 1] < seg_offsets[i]) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (at %lld)", (long long)i);
+    const double t_begin = Trace::now();
+    g_tr.t_stage = g_tr.t_wait = g_tr.t_fetch = 0;
+    g_tr.t_check = Trace::now() - t_begin;
     CUDA_TRY(cudaSetDevice(h->device));
     memset(h->stats, 0, sizeof h->stats);
     h->ties_host.clear();
@@ -626,7 +701,7 @@ int sct_match(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offset
         return SCT_OK;
     };
     while (first < n) {
-        int64_t cn = std::min<int64_t>(h->chunk_segs, n - first);
+        int64_t cn = std::min<int64_t>(h->stream_segs, n - first);
         const int64_t limit = seg_offsets[first] + h->chunk_bytes;
         if (seg_offsets[first + cn] > limit) {
             const int64_t *e = std::upper_bound(seg_offsets + first, seg_offsets + first + cn + 1, limit);
@@ -646,6 +721,10 @@ int sct_match(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offset
     tie_offsets[n] = tie_base;
     *tie_ids = h->ties_host.empty() ? nullptr : h->ties_host.data();
     *n_tie_ids = tie_base;
+    if (g_tr.on)
+        fprintf(stderr, "[sct_match] n=%lld chunks=%lld total %.3f ms: check %.3f stage %.3f wait %.3f fetch %.3f\n",
+                (long long)n, (long long)chunk, 1e3 * (Trace::now() - t_begin), 1e3 * g_tr.t_check, 1e3 * g_tr.t_stage,
+                1e3 * g_tr.t_wait, 1e3 * g_tr.t_fetch);
     return SCT_OK;
 }
 
