@@ -41,13 +41,13 @@ N_SEGMENTS = 1_000_000
 MAX_ERROR = 2
 THREADS_FLAG = 16          # the reference's default -t (fixes k = 2; irrelevant for the clean ACGT bench data)
 OPS_PER_COLUMN = 14        # LOP3/IADD3-fused Hyyro column update
-CPU_SAMPLE = 200_000       # segments per CPU-arm step / cpu_baseline sample
+CPU_SAMPLE = 1_000_000     # segments per CPU-arm step / cpu_baseline sample (the whole per-GPU workload)
 
 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--segments", type=int, default=N_SEGMENTS, help=argparse.SUPPRESS)
@@ -63,37 +63,86 @@ def workload_name(a):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons sampled DURING the timed region: an in-process NVML polling thread (every 2 ms —
+    the timed region of this workload is tens of milliseconds, too short for `nvidia-smi -lms`); falls back to the
+    nvidia-smi recipe of B200_PROFILING.md when NVML cannot be loaded."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.index = index
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-        self.p = None
+        self.sm, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        self._smi = None
+        self._nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self._nv = pynvml
+        except Exception:
+            self._nv = None
+
+    @staticmethod
+    def _physical_index(i):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [x for x in vis.split(",") if x != ""]
+            if i < len(ids) and ids[i].isdigit():
+                return int(ids[i])
+        return i
+
+    def _poll(self):
+        nv = self._nv
+        bits = (("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40),
+                ("sw_power_cap", 0x4))          # nvmlClocksEventReason* bit values
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                for name, bit in bits:
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.002)
 
     def start(self):
+        if self._nv is not None:
+            self._thread = threading.Thread(target=self._poll, daemon=True)
+            self._thread.start()
+            return
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
-                                      stderr=subprocess.DEVNULL)
+            self._f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+            self._smi = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self._f,
+                                         stderr=subprocess.DEVNULL)
         except OSError:
-            self.p = None
+            self._smi = None
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.p is None:
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "how": None}
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join(timeout=2)
+            if self.sm:
+                out.update(sm_mhz=float(np.median(self.sm)), sm_max_mhz=self.max_mhz, reasons=sorted(self.reasons),
+                           samples=len(self.sm), how="NVML polled every 2 ms inside the timed region")
             return out
-        self.p.terminate()
+        if self._smi is None:
+            return out
+        self._smi.terminate()
         try:
-            self.p.wait(timeout=5)
+            self._smi.wait(timeout=5)
         except subprocess.TimeoutExpired:
-            self.p.kill()
-        self.f.flush()
-        self.f.seek(0)
+            self._smi.kill()
+        self._f.flush()
+        self._f.seek(0)
         sm, mx, reasons = [], [], set()
-        for line in self.f.read().splitlines():
+        for line in self._f.read().splitlines():
             c = [x.strip() for x in line.split(",")]
             if len(c) < 9:
                 continue
@@ -106,11 +155,12 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         try:
-            os.unlink(self.f.name)
+            os.unlink(self._f.name)
         except OSError:
             pass
         if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm),
+                       how="nvidia-smi -lms 100 during the timed region")
         return out
 
 
