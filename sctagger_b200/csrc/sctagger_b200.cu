@@ -16,7 +16,10 @@
 #include <new>
 #include <string>
 #include <thread>
-#include <omp.h>
+#include <mutex>
+#include <condition_variable>
+#include <functional>
+#include <atomic>
 #include <vector>
 
 using namespace sct;
@@ -64,18 +67,90 @@ inline uint8_t comp_char(uint8_t c) {                                           
 }
 inline bool is_acgt(uint8_t c) { return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }
 
-// memcpy split over the handle's host worker threads (-t): staging and un-staging are the host-serial part of sct_match
-void par_memcpy(void *dst, const void *src, size_t bytes, int nt) {
-    if (nt <= 1 || bytes < (1u << 20)) {
-        memcpy(dst, src, bytes);
+// Host worker threads (-t) for staging / un-staging.  A small fork-join pool with PASSIVE waiting: with one process (or
+// one handle) per GPU, eight of these run side by side, and spinning waiters (OpenMP's default) starve each other.
+class HostPool {
+public:
+    explicit HostPool(int n_threads) : n_(std::max(1, n_threads)) {
+        for (int t = 1; t < n_; ++t) workers_.emplace_back([this, t] { loop(t); });
+    }
+    ~HostPool() {
+        {
+            std::lock_guard<std::mutex> g(m_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto &w : workers_) w.join();
+    }
+    int size() const { return n_; }
+    // fn(t) for t = 0..size()-1, t = 0 on the calling thread; returns when all are done
+    void run(const std::function<void(int)> &fn) {
+        if (n_ == 1) {
+            fn(0);
+            return;
+        }
+        {
+            std::lock_guard<std::mutex> g(m_);
+            fn_ = &fn;
+            pending_ = n_ - 1;
+            ++epoch_;
+        }
+        cv_.notify_all();
+        fn(0);
+        std::unique_lock<std::mutex> g(m_);
+        done_.wait(g, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+
+private:
+    void loop(int t) {
+        unsigned long long seen = 0;
+        for (;;) {
+            const std::function<void(int)> *fn;
+            {
+                std::unique_lock<std::mutex> g(m_);
+                cv_.wait(g, [&] { return stop_ || epoch_ != seen; });
+                if (stop_) return;
+                seen = epoch_;
+                fn = fn_;
+            }
+            (*fn)(t);
+            {
+                std::lock_guard<std::mutex> g(m_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+    int n_;
+    std::vector<std::thread> workers_;
+    std::mutex m_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)> *fn_ = nullptr;
+    int pending_ = 0;
+    unsigned long long epoch_ = 0;
+    bool stop_ = false;
+};
+
+// [0, n) split into pool.size() contiguous ranges: fn(first, last)
+template <class F>
+void par_ranges(HostPool *pool, int64_t n, int64_t min_per_thread, F fn) {
+    const int nt = pool ? (int)std::min<int64_t>(pool->size(), std::max<int64_t>(1, n / std::max<int64_t>(1, min_per_thread))) : 1;
+    if (nt <= 1) {
+        fn((int64_t)0, n);
         return;
     }
-    const size_t piece = ((bytes + nt - 1) / nt + 63) & ~(size_t)63;
-#pragma omp parallel for num_threads(nt) schedule(static)
-    for (int t = 0; t < nt; ++t) {
-        const size_t a = std::min(bytes, piece * t), b = std::min(bytes, piece * (t + 1));
-        if (b > a) memcpy((char *)dst + a, (const char *)src + a, b - a);
-    }
+    const int64_t piece = (n + nt - 1) / nt;
+    pool->run([&](int t) {
+        if (t >= nt) return;
+        const int64_t a = std::min(n, piece * t), b = std::min(n, piece * (t + 1));
+        if (b > a) fn(a, b);
+    });
+}
+
+void par_memcpy(HostPool *pool, void *dst, const void *src, size_t bytes) {
+    par_ranges(pool, (int64_t)bytes, 1 << 19, [&](int64_t a, int64_t b) {
+        memcpy((char *)dst + a, (const char *)src + a, (size_t)(b - a));
+    });
 }
 
 template <class T>
@@ -137,6 +212,7 @@ struct sct_handle {
     int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
     int64_t stream_segs = 0;                    // segments per streamed chunk of sct_match (<= chunk_segs)
     int host_threads = 1;        // worker threads for staging / un-staging (from -t, capped)
+    HostPool *pool = nullptr;
     int tie_per_seg = 8;
     int seed_ctas_per_sm = 6;
     uint32_t *d_ovf_scratch = nullptr;
@@ -386,16 +462,19 @@ int start_chunk(sct_handle *h, Slot &s, const uint8_t *seg_bytes, const int64_t 
     if (nbytes < 0) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
     TRY(ensure_slot(h, s, n, nbytes));
     const double t0 = Trace::now();
-    if (nbytes > 0) par_memcpy(s.h_bytes, seg_bytes + b0, (size_t)nbytes, h->host_threads);
+    if (nbytes > 0) par_memcpy(h->pool, s.h_bytes, seg_bytes + b0, (size_t)nbytes);
     {
         long long *dst = s.h_off;
         const int64_t *src = off + first;
-        bool bad = false;
-#pragma omp parallel for num_threads(h->host_threads) schedule(static) reduction(|| : bad) if (n > (1 << 16))
-        for (int64_t i = 0; i <= n; ++i) {
-            dst[i] = src[i] - b0;
-            if (i < n && src[i + 1] < src[i]) bad = true;
-        }
+        std::atomic<bool> bad(false);
+        par_ranges(h->pool, n + 1, 1 << 16, [&](int64_t a, int64_t b) {
+            bool mine = false;
+            for (int64_t i = a; i < b; ++i) {
+                dst[i] = src[i] - b0;
+                if (i < n && src[i + 1] < src[i]) mine = true;
+            }
+            if (mine) bad = true;
+        });
         if (bad) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
     }
     g_tr.t_stage += Trace::now() - t0;
@@ -427,18 +506,19 @@ int fetch_results(sct_handle *h, Slot &s, int32_t *min_ed, int32_t *n_ties, int6
         g_tr.t_wait += Trace::now() - t0;
         t0 = Trace::now();
         h->stats[4] += n * 8 + (n + 1) * 8 + total * 4;
-        par_memcpy(min_ed + out_first, s.h_min, (size_t)n * sizeof(int), h->host_threads);
-        par_memcpy(n_ties + out_first, s.h_nt, (size_t)n * sizeof(int), h->host_threads);
+        par_memcpy(h->pool, min_ed + out_first, s.h_min, (size_t)n * sizeof(int));
+        par_memcpy(h->pool, n_ties + out_first, s.h_nt, (size_t)n * sizeof(int));
         {
             int64_t *dst = tie_offsets + out_first;
             const long long *src = s.h_toff;
-#pragma omp parallel for num_threads(h->host_threads) schedule(static) if (n > (1 << 16))
-            for (int64_t i = 0; i < n; ++i) dst[i] = tie_base + src[i];
+            par_ranges(h->pool, n, 1 << 16, [&](int64_t a, int64_t b) {
+                for (int64_t i = a; i < b; ++i) dst[i] = tie_base + src[i];
+            });
         }
         if (total > 0) {
             const size_t at = h->ties_host.size();
             h->ties_host.resize(at + (size_t)total);
-            par_memcpy(h->ties_host.data() + at, s.h_ties, (size_t)total * sizeof(int), h->host_threads);
+            par_memcpy(h->pool, h->ties_host.data() + at, s.h_ties, (size_t)total * sizeof(int));
         }
         g_tr.t_fetch += Trace::now() - t0;
     }
@@ -452,6 +532,8 @@ int fetch_results(sct_handle *h, Slot &s, int32_t *min_ed, int32_t *n_ties, int6
 
 extern "C" {
 
+int sct_device_count(void);
+static int ndev_visible() { return sct_device_count(); }
 int sct_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) {
@@ -497,7 +579,9 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
     h->threads = threads;
     h->kpre = kpre;
     h->mem_gb = mem_gb;
-    h->host_threads = std::max(1, std::min({(int)threads, 8, (int)std::thread::hardware_concurrency()}));
+    // -t host threads, at most 8, and no more than this GPU's share of the host cores (one handle per GPU)
+    h->host_threads = std::max(1, std::min({(int)threads, 8, (int)std::thread::hardware_concurrency() / std::max(1, ndev_visible())}));
+    h->pool = new (std::nothrow) HostPool(h->host_threads);
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     h->sm_count = prop.multiProcessorCount;
@@ -625,6 +709,7 @@ int sct_destroy(sct_handle *h) {
     dev_free(h->d_tabF); dev_free(h->d_tabR); dev_free(h->d_patF); dev_free(h->d_patR);
     dev_free(h->d_ovf_scratch); dev_free(h->d_flush);
     dev_free(h->d_boff); dev_free(h->d_ewords); dev_free(h->d_eids);
+    delete h->pool;
     delete h;
     return SCT_OK;
 }
