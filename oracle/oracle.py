@@ -75,3 +75,35 @@ def match(barcodes: np.ndarray, seg_bytes: np.ndarray, offsets: np.ndarray, max_
     tie_ids = np.ctypeslib.as_array(ids, shape=(max(total, 1),))[:total].copy()
     L.sct_oracle_free(ids)
     return min_ed[:n], n_ties[:n], tie_off, tie_ids
+
+
+def align(adapter: bytes, read_bytes: np.ndarray, offsets: np.ndarray, workers: int = 0, algo: str = "dp"):
+    """Adapter alignment oracle (oracle/align_oracle.c; PARITY UNPINNED, see its header): what the reference's
+    get_alns (scTagger.py:176-196) returns for every read, as arrays:
+    (strand int8[n] ('+', '-' as ASCII, 0 = 'NA'), dist int32[n] (-1 = NA), loc_offsets int64[n+1], locs int32[total])."""
+    L = lib()
+    fn = {"dp": L.sct_oracle_align, "bv": L.sct_oracle_align_bv}[algo]
+    u8p = ctypes.POINTER(ctypes.c_uint8)
+    i32p = ctypes.POINTER(ctypes.c_int32)
+    fn.restype = ctypes.c_int
+    fn.argtypes = [u8p, ctypes.c_int, u8p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64, ctypes.c_int,
+                   ctypes.POINTER(ctypes.c_int8), i32p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(i32p)]
+    ad = np.frombuffer(bytes(adapter), dtype=np.uint8).copy()
+    read_bytes = np.ascontiguousarray(read_bytes, dtype=np.uint8)
+    if read_bytes.size == 0:
+        read_bytes = np.zeros(1, dtype=np.uint8)
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    n = offsets.shape[0] - 1
+    strand = np.zeros(max(n, 1), dtype=np.int8)
+    dist = np.empty(max(n, 1), dtype=np.int32)
+    loc_off = np.zeros(n + 1, dtype=np.int64)
+    ids = i32p()
+    rc = fn(_ptr(ad, ctypes.c_uint8), int(ad.size), _ptr(read_bytes, ctypes.c_uint8), _ptr(offsets, ctypes.c_int64), n,
+            int(workers), _ptr(strand, ctypes.c_int8), _ptr(dist, ctypes.c_int32), _ptr(loc_off, ctypes.c_int64),
+            ctypes.byref(ids))
+    if rc != 0:
+        raise RuntimeError(f"align oracle failed with code {rc}")
+    total = int(loc_off[n])
+    locs = np.ctypeslib.as_array(ids, shape=(max(total, 1),))[:total].copy()
+    L.sct_oracle_free(ids)
+    return strand[:n], dist[:n], loc_off, locs

@@ -149,3 +149,64 @@ def write_segments(path, seg_bytes: np.ndarray, offsets: np.ndarray, first_index
                 f.write(b"".join(buf))
                 buf = []
         f.write(b"".join(buf))
+
+
+ADAPTER = b"CTACACGACGCTCTTCCGATCT"   # reference default -sa (scTagger.py:42)
+
+
+def make_reads(n_reads: int, seed: int, adapter: bytes = ADAPTER, median_len: int = 900, min_len: int = 200,
+               max_len: int = 5000):
+    """BASELINE config 5: long reads with log-normal lengths (median 900, clipped 200..5000), uniform
+    ACGT; 85 % carry the adapter with 8 % per-base errors — forward near the 5' end (offset U[10,60]) or reverse-
+    complemented near the 3' end, 50/50 — followed by 16 + 12 random bases and T x 30.
+    Returns (read_bytes uint8[sum len], offsets int64[n+1])."""
+    rng = np.random.default_rng(seed + 15485863)
+    lens = np.clip(np.exp(rng.normal(np.log(median_len), 0.6, size=n_reads)), min_len, max_len).astype(np.int64)
+    offsets = np.zeros(n_reads + 1, dtype=np.int64)
+    np.cumsum(lens, out=offsets[1:])
+    out = ACGT[rng.integers(0, 4, size=int(offsets[-1]))]
+    ad = np.frombuffer(adapter, dtype=np.uint8)
+    m = ad.size
+    has = rng.random(n_reads) < 0.85
+    rev = rng.random(n_reads) < 0.5
+    off5 = rng.integers(10, 61, size=n_reads)
+    W = m + 8                                   # room for insertions
+    for r in np.nonzero(has)[0]:
+        # mutate the adapter: per-base sub / ins / del with total rate 8 %
+        a = []
+        for ch in ad:
+            u = rng.random()
+            if u < 0.08 / 3:
+                a.append(int(ACGT[rng.integers(0, 4)]))
+            elif u < 2 * 0.08 / 3:
+                a.append(int(ch))
+                a.append(int(ACGT[rng.integers(0, 4)]))
+            elif u < 0.08:
+                continue
+            else:
+                a.append(int(ch))
+        a = a[:W]
+        block = np.concatenate([np.array(a, dtype=np.uint8), ACGT[rng.integers(0, 4, size=28)],
+                                np.full(30, ord("T"), dtype=np.uint8)])
+        L = int(lens[r])
+        block = block[: max(0, L - int(off5[r]))]
+        if rev[r]:
+            block = _COMP[block[::-1]]
+            s = int(offsets[r + 1]) - int(off5[r]) - block.size
+        else:
+            s = int(offsets[r]) + int(off5[r])
+        out[s:s + block.size] = block
+    return out, offsets
+
+
+def write_fastq(path, read_bytes: np.ndarray, offsets: np.ndarray, first_index: int = 0):
+    raw = read_bytes.tobytes()
+    with _open_w(path) as f:
+        buf = []
+        for i in range(offsets.shape[0] - 1):
+            s = raw[offsets[i]:offsets[i + 1]]
+            buf.append(b"@read%d some description\n%s\n+\n%s\n" % (first_index + i, s, b"I" * len(s)))
+            if len(buf) >= 16384:
+                f.write(b"".join(buf))
+                buf = []
+        f.write(b"".join(buf))

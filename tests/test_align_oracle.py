@@ -1,0 +1,61 @@
+"""CPU: the two restatements of edlib's HW semantics for extract_lr_bc (plain DP and Myers bit-vector,
+oracle/align_oracle.c) agree with each other and with hand-derived cases.  Parity with edlib itself is UNPINNED:
+edlib is not present in this environment."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from sctagger_b200 import synth
+
+
+def _pack(reads):
+    off = np.zeros(len(reads) + 1, np.int64)
+    np.cumsum([len(r) for r in reads], out=off[1:])
+    return np.frombuffer(b"".join(reads), np.uint8), off
+
+
+def _as_tuples(res):
+    s, d, lo, locs = res
+    return [(chr(s[i]) if s[i] else "NA", int(d[i]), locs[lo[i]:lo[i + 1]].tolist()) for i in range(len(d))]
+
+
+def test_hand_cases():
+    a1 = b"ACGTT"                     # a2 = AACGT
+    reads = [b"GGACGTTGG",            # exact a1 ending at index 6
+             b"GGAACGTGG",            # exact a2 starting at index 2 -> loc = 2 - 9 - 1 = -8
+             b"",                     # empty: both distances m -> NA
+             b"GGGGGG",               # equal distances -> NA
+             b"ACGTTACGTT",           # a1 twice: ends 4 and 9
+             b"TTACGTCC"]             # a1 with one deletion ...
+    got = _as_tuples(oracle.align(a1, *_pack(reads)))
+    assert got[0] == ("+", 0, [6])
+    assert got[1] == ("-", 0, [-8])
+    assert got[2] == ("NA", -1, [])
+    assert got[3] == ("NA", -1, [])
+    assert got[4] == ("+", 0, [4, 9])
+    assert got == _as_tuples(oracle.align(a1, *_pack(reads), algo="bv"))
+
+
+@pytest.mark.parametrize("seed,adapter", [(1, synth.ADAPTER), (2, b"ACGTACGTAC"), (3, b"GATTACAGATTACAGATTACAGATTACAGAT"), (4, b"ANCGT")])
+def test_dp_equals_bitvector(seed, adapter):
+    rb, off = synth.make_reads(300, seed, adapter=adapter if b"N" not in adapter else synth.ADAPTER, median_len=300,
+                               min_len=1, max_len=900)
+    rb = rb.copy()
+    rng = np.random.default_rng(seed)
+    rb[rng.integers(0, rb.size, size=50)] = ord("N")          # literal comparison: N only equals N
+    rb[rng.integers(0, rb.size, size=50)] = ord("a")
+    a = oracle.align(adapter, rb, off, algo="dp")
+    b = oracle.align(adapter, rb, off, algo="bv")
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    assert (a[0] != 0).sum() > 20
+
+
+def test_cfg5_generator_shape():
+    rb, off = synth.make_reads(2000, synth.SEEDS["cfg5"])
+    lens = np.diff(off)
+    assert lens.min() >= 200 and lens.max() <= 5000 and 700 < np.median(lens) < 1100
+    s, d, lo, locs = oracle.align(synth.ADAPTER, rb, off, algo="bv")
+    found = (d >= 0) & (d <= 5)
+    assert 0.7 < found.mean() < 0.95            # ~85 % of reads carry a recognisable adapter
+    assert 0.35 < (s[found] == ord("+")).mean() < 0.65
