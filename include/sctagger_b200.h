@@ -116,6 +116,38 @@ int sct_measure_int32_peak(int device, int mode, int repeats, double *lane_ops_p
 /* Wipe L2 by overwriting a buffer larger than it (used between timed bench iterations). */
 int sct_flush_l2(sct_handle *h);
 
+/* ---------------------------------------------------------------------------------------------------------------------
+ * extract_lr_bc adapter alignment (BASELINE config 5).  The reference's seam is
+ *     get_lr_bc_alns(seqs, threads) -> [(strand, dist, locs)]                         reference scTagger.py:307-314
+ * which maps get_alns (scTagger.py:176-196) over the reads: two edlib.align(a, seq, 'HW', 'locations') calls per read,
+ * a1 = the short-read adapter (-sa, scTagger.py:41-43) and a2 = rev_compl(a1) (scTagger.py:363-365), characters compared
+ * literally.  edlib is a third-party dependency that is not part of the reference tree (env.yaml:9, unpinned); the
+ * semantics implemented here are the ones restated in SURVEY.md Appendix B / oracle/align_oracle.c (parity unpinned).
+ *
+ *   sct_align_create  <- the globals a1/a2 (scTagger.py:363-365) and -t
+ *   sct_align         <- get_lr_bc_alns: per read
+ *        strand[r]   '+' (a1 strictly better), '-' (a2 strictly better) or 0 (equal distances: the reference's 'NA')
+ *        dist[r]     the smaller edit distance, or -1 for 'NA'
+ *        locs        '+': every 0-based end position of a1 at that distance (scTagger.py:185)
+ *                    '-': start - len(seq) - 1 for every location of a2 (scTagger.py:189), start = edlib's start of the
+ *                         location = the leftmost start with the same distance for that end
+ *                    locations of read r are (*locs)[loc_offsets[r] .. loc_offsets[r+1]); none for 'NA'
+ *   Adapter length <= 32.  Host buffers in, host buffers out; *locs is library-owned until the next call / destroy.
+ */
+typedef struct sct_align_handle sct_align_handle;
+int sct_align_create(int device, const uint8_t *adapter, int32_t adapter_length, int32_t threads, double mem_gb,
+                     sct_align_handle **out);
+int sct_align_destroy(sct_align_handle *h);
+int sct_align(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *read_offsets, int64_t n,
+              int8_t *strand, int32_t *dist, int64_t *loc_offsets, const int32_t **locs, int64_t *n_locs);
+/* Device-resident variant for timing: one batch (one chunk) staged once, then passes timed with CUDA events. */
+int sct_align_stage(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *read_offsets, int64_t n);
+int sct_align_run_staged(sct_align_handle *h, float *pass_ms, float *pass1_kernel_ms);
+/* [0] kernel launches, [1] chunks, [2] host->device bytes, [3] device->host bytes, [4] device time of the passes in ns,
+ * [5] reads, [6..7] reserved.   Options: "chunk_bytes", "chunk_reads". */
+int sct_align_stats(sct_align_handle *h, int64_t stats[8]);
+int sct_align_set_option(sct_align_handle *h, const char *key, int64_t value);
+
 #ifdef __cplusplus
 }
 #endif

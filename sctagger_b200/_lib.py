@@ -19,6 +19,8 @@ EXPORTS = (
     "sct_device_count", "sct_last_error", "sct_create", "sct_destroy", "sct_match", "sct_stage",
     "sct_run_staged", "sct_fetch_staged", "sct_stats", "sct_set_option", "sct_chunk_capacity",
     "sct_measure_int32_peak", "sct_flush_l2",
+    "sct_align_create", "sct_align_destroy", "sct_align", "sct_align_stage", "sct_align_run_staged",
+    "sct_align_stats", "sct_align_set_option",
 )
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
@@ -75,6 +77,22 @@ def lib():
                                                  ctypes.POINTER(ctypes.c_double)]
             L.sct_flush_l2.restype = ctypes.c_int
             L.sct_flush_l2.argtypes = [_vp]
+            _i8p = ctypes.POINTER(ctypes.c_int8)
+            L.sct_align_create.restype = ctypes.c_int
+            L.sct_align_create.argtypes = [ctypes.c_int, _u8p, ctypes.c_int32, ctypes.c_int32, ctypes.c_double,
+                                           ctypes.POINTER(_vp)]
+            L.sct_align_destroy.restype = ctypes.c_int
+            L.sct_align_destroy.argtypes = [_vp]
+            L.sct_align.restype = ctypes.c_int
+            L.sct_align.argtypes = [_vp, _u8p, _i64p, ctypes.c_int64, _i8p, _i32p, _i64p, ctypes.POINTER(_i32p), _i64p]
+            L.sct_align_stage.restype = ctypes.c_int
+            L.sct_align_stage.argtypes = [_vp, _u8p, _i64p, ctypes.c_int64]
+            L.sct_align_run_staged.restype = ctypes.c_int
+            L.sct_align_run_staged.argtypes = [_vp, _f32p, _f32p]
+            L.sct_align_stats.restype = ctypes.c_int
+            L.sct_align_stats.argtypes = [_vp, _i64p]
+            L.sct_align_set_option.restype = ctypes.c_int
+            L.sct_align_set_option.argtypes = [_vp, ctypes.c_char_p, ctypes.c_int64]
             _lib = L
     return _lib
 
@@ -195,6 +213,112 @@ class Matcher:
 
     def flush_l2(self):
         _check(lib().sct_flush_l2(self._h))
+
+
+ALIGN_STAT_NAMES = ("launches", "chunks", "h2d_bytes", "d2h_bytes", "device_ns", "reads", "reserved6", "reserved7")
+
+
+class Aligner:
+    """One handle = one GPU holding the adapter's Myers tables (sct_align_create .. sct_align_destroy): the
+    `get_lr_bc_alns` seam of extract_lr_bc (reference scTagger.py:307-314, 176-196)."""
+
+    def __init__(self, adapter: bytes, threads: int = 1, mem_gb: float = 16.0, device: int = 0, **options):
+        ad = np.frombuffer(bytes(adapter), dtype=np.uint8).copy()
+        self._h = _vp()
+        self.device = int(device)
+        _check(lib().sct_align_create(int(device), _ptr(_as_u8(ad), ctypes.c_uint8), int(ad.size), int(threads),
+                                      float(mem_gb), ctypes.byref(self._h)))
+        for k, v in options.items():
+            _check(lib().sct_align_set_option(self._h, k.encode(), int(v)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().sct_align_destroy(self._h)
+            self._h = _vp()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def align(self, read_bytes: np.ndarray, offsets: np.ndarray):
+        """-> (strand int8[n] ('+'/'-' as ASCII, 0 = NA), dist int32[n] (-1 = NA), loc_offsets int64[n+1], locs int32[])"""
+        rb = _as_u8(read_bytes)
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        n = off.shape[0] - 1
+        strand = np.empty(max(n, 1), dtype=np.int8)
+        dist = np.empty(max(n, 1), dtype=np.int32)
+        loc_off = np.empty(n + 1, dtype=np.int64)
+        ids = _i32p()
+        total = ctypes.c_int64(0)
+        _check(lib().sct_align(self._h, _ptr(rb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), n,
+                               _ptr(strand, ctypes.c_int8), _ptr(dist, ctypes.c_int32), _ptr(loc_off, ctypes.c_int64),
+                               ctypes.byref(ids), ctypes.byref(total)))
+        t = int(total.value)
+        locs = np.ctypeslib.as_array(ids, shape=(t,)).copy() if t else np.zeros(0, dtype=np.int32)
+        return strand[:n], dist[:n], loc_off, locs
+
+    def stage(self, read_bytes: np.ndarray, offsets: np.ndarray):
+        rb = _as_u8(read_bytes)
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        _check(lib().sct_align_stage(self._h, _ptr(rb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), off.shape[0] - 1))
+
+    def run_staged(self):
+        a, b = ctypes.c_float(0), ctypes.c_float(0)
+        _check(lib().sct_align_run_staged(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return float(a.value), float(b.value)
+
+    def stats(self) -> dict:
+        s = np.zeros(8, dtype=np.int64)
+        _check(lib().sct_align_stats(self._h, _ptr(s, ctypes.c_int64)))
+        return dict(zip(ALIGN_STAT_NAMES, s.tolist()))
+
+
+def align_reads(adapter: bytes, read_bytes: np.ndarray, offsets: np.ndarray, threads: int = 1, mem_gb: float = 16.0,
+                devices=None, **options):
+    """All reads against the adapter and its reverse complement on one or several GPUs (contiguous read ranges, one
+    host thread + one handle per GPU, concatenated in read order; no collective)."""
+    if devices is None:
+        devices = [0]
+    elif isinstance(devices, int):
+        devices = list(range(devices))
+    devices = list(devices)
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    n = offsets.shape[0] - 1
+    if len(devices) == 1:
+        with Aligner(adapter, threads, mem_gb, devices[0], **options) as a:
+            return a.align(read_bytes, offsets)
+    bounds = shard_bounds(n, len(devices))
+    results = [None] * len(devices)
+    errors = []
+
+    def work(i):
+        try:
+            lo, hi = bounds[i]
+            with Aligner(adapter, threads, mem_gb / len(devices), devices[i], **options) as a:
+                results[i] = a.align(read_bytes, offsets[lo:hi + 1])
+        except Exception as e:
+            errors.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(len(devices))]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    if errors:
+        raise errors[0]
+    strand = np.concatenate([r[0] for r in results])
+    dist = np.concatenate([r[1] for r in results])
+    locs = np.concatenate([r[3] for r in results])
+    offs, base = [], 0
+    for r in results:
+        offs.append(r[2][:-1] + base)
+        base += int(r[2][-1])
+    offs.append(np.array([base], dtype=np.int64))
+    return strand, dist, np.concatenate(offs), locs
 
 
 def measure_int32_peak(device: int = 0, mode: int = 0, repeats: int = 10) -> float:

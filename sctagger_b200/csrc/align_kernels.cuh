@@ -1,0 +1,283 @@
+// sm_100a kernels of the `extract_lr_bc` adapter alignment (reference scTagger.py:176-196 get_alns: two
+// edlib.align(adapter, read, 'HW', 'locations') calls per read, adapter and its reverse complement).
+//
+// One thread owns one read and advances BOTH adapters' Myers/Hyyro bit-vectors (pattern <= 32 characters: one register
+// each) over the read, one column per base:
+//     Xv = Eq | Mv;  Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;  Ph = Mv | ~(Xh | Pv);  Mh = Pv & Xh
+//     score += Ph[m-1] - Mh[m-1];  Ph <<= 1;  Mh <<= 1;  Pv = Mh | ~(Xv | Ph);  Mv = Ph & Xv        (free top row: HW)
+// Eq comes from a 256-entry table indexed by the raw byte (literal comparison like edlib: N only equals N), both adapters
+// interleaved so that one LDS.64 serves a column.  Reads are fetched as aligned 128-bit words.
+//   pass 1: minimum distance and number of end positions at the minimum per adapter -> strand, distance, #locations
+//   (exclusive scan of #locations)
+//   pass 2: the winning adapter again, emitting the locations the reference derives (scTagger.py:184-191):
+//           '+' : every end position at the minimum;
+//           '-' : for every such end the LEFTMOST start with the same distance (edlib's start location: reversed
+//                 adapter against the reversed read prefix, prefix-anchored, last optimal column), as start - len - 1.
+// Reads of one chunk are processed in descending length order (counting sort on len/32) so that the 32 reads of a warp
+// are of similar length.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace sct {
+
+constexpr int ALN_THREADS = 128;
+constexpr int ALN_BUCKETS = 1024;        // length buckets of 32 bases; longer reads share the last bucket
+
+struct AlignParams {
+    const uint8_t *bytes;                // read bytes of the chunk; the allocation is 16-byte aligned and padded
+    const long long *off;                // n + 1 offsets
+    int n;
+    int m;                               // adapter length (<= 32)
+    const uint2 *peq;                    // [256] {Eq of a1, Eq of a2} by byte value
+    const uint32_t *rpeq2;               // [256] Eq of reversed a2 (start search)
+    const int *order;                    // read ids, long reads first
+    signed char *strand;                 // '+', '-', 0 = NA
+    int *dist;                           // -1 = NA
+    int *n_locs;
+    const long long *loc_off;            // exclusive scan of n_locs (pass 2)
+    int *locs;
+    unsigned long long loc_cap;
+};
+
+// ---- length ordering ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int len_bucket(long long len) {
+    const long long b = len >> 5;
+    return ALN_BUCKETS - 1 - (int)(b < ALN_BUCKETS - 1 ? b : ALN_BUCKETS - 1);   // descending length
+}
+
+__global__ void __launch_bounds__(256) aln_hist_kernel(const long long *__restrict__ off, int n, unsigned int *__restrict__ hist) {
+    __shared__ unsigned int sh[ALN_BUCKETS];
+    for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        atomicAdd(&sh[len_bucket(off[i + 1] - off[i])], 1u);
+    __syncthreads();
+    for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x)
+        if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+// one block of ALN_BUCKETS threads: exclusive scan of the histogram in place -> bucket cursors
+__global__ void __launch_bounds__(ALN_BUCKETS) aln_bucket_scan_kernel(unsigned int *__restrict__ hist) {
+    __shared__ unsigned int sh[ALN_BUCKETS];
+    const unsigned int v = hist[threadIdx.x];
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < ALN_BUCKETS; o <<= 1) {
+        const unsigned int t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0u;
+        __syncthreads();
+        sh[threadIdx.x] += t;
+        __syncthreads();
+    }
+    hist[threadIdx.x] = sh[threadIdx.x] - v;
+}
+
+__global__ void __launch_bounds__(256) aln_scatter_kernel(const long long *__restrict__ off, int n, unsigned int *__restrict__ cursor,
+                                                          int *__restrict__ order) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    order[atomicAdd(&cursor[len_bucket(off[i + 1] - off[i])], 1u)] = i;
+}
+
+// ---- Myers column ---------------------------------------------------------------------------------------------------
+struct Myers {
+    uint32_t Pv, Mv;
+    int score;
+    __device__ __forceinline__ void init(int m) {
+        Pv = m >= 32 ? 0xFFFFFFFFu : ((1u << m) - 1u);
+        Mv = 0u;
+        score = m;
+    }
+    // HW: free top row (horizontal delta 0 enters at the top);  PREFIX: top row grows by one per column (+1 enters)
+    template <bool PREFIX>
+    __device__ __forceinline__ void step(uint32_t Eq, uint32_t top) {
+        const uint32_t Xv = Eq | Mv;
+        const uint32_t Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
+        uint32_t Ph = Mv | ~(Xh | Pv);
+        uint32_t Mh = Pv & Xh;
+        score += (Ph & top) ? 1 : 0;
+        score -= (Mh & top) ? 1 : 0;
+        Ph = (Ph << 1) | (PREFIX ? 1u : 0u);
+        Mh <<= 1;
+        Pv = Mh | ~(Xv | Ph);
+        Mv = Ph & Xv;
+    }
+};
+
+// Calls f(byte, position) for every byte of [beg, end) using aligned 128-bit loads (the buffer is padded).
+template <class F>
+__device__ __forceinline__ void for_each_byte(const uint8_t *__restrict__ bytes, long long beg, long long end, F f) {
+    long long w = beg & ~15ll;
+    for (; w < end; w += 16) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bytes + w));
+        const uint32_t q[4] = {v.x, v.y, v.z, v.w};
+        if (w >= beg && w + 16 <= end) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) f((q[k >> 2] >> (8 * (k & 3))) & 0xFFu, w + k);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+                if (w + k >= beg && w + k < end) f((q[k >> 2] >> (8 * (k & 3))) & 0xFFu, w + k);
+        }
+    }
+}
+
+// ---- pass 1 ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(ALN_THREADS) aln_pass1_kernel(const AlignParams p) {
+    __shared__ uint2 s_peq[256];
+    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) s_peq[i] = p.peq[i];
+    __syncthreads();
+    const int t = blockIdx.x * ALN_THREADS + threadIdx.x;
+    if (t >= p.n) return;
+    const int r = p.order[t];
+    const long long beg = p.off[r], end = p.off[r + 1];
+    const int m = p.m;
+    const uint32_t top = 1u << (m - 1);
+    Myers a, b;
+    a.init(m);
+    b.init(m);
+    int best1 = 1 << 20, best2 = 1 << 20, c1 = 0, c2 = 0;
+    for_each_byte(p.bytes, beg, end, [&](uint32_t ch, long long) {
+        const uint2 e = s_peq[ch];
+        a.step<false>(e.x, top);
+        b.step<false>(e.y, top);
+        if (a.score < best1) { best1 = a.score; c1 = 0; }
+        c1 += a.score == best1;
+        if (b.score < best2) { best2 = b.score; c2 = 0; }
+        c2 += b.score == best2;
+    });
+    if (end == beg) best1 = best2 = m;       // edlib: empty target -> distance = query length (both adapters: a tie)
+    signed char s = 0;
+    int d = -1, nl = 0;
+    if (best1 < best2) { s = '+'; d = best1; nl = c1; }
+    else if (best2 < best1) { s = '-'; d = best2; nl = c2; }
+    p.strand[r] = s;
+    p.dist[r] = d;
+    p.n_locs[r] = nl;
+}
+
+// ---- pass 2 ---------------------------------------------------------------------------------------------------------
+// leftmost start s with Levenshtein(a2, read[s..e]) == d: reversed a2 against read[e], read[e-1], ... prefix-anchored
+__device__ __forceinline__ long long leftmost_start(const uint8_t *__restrict__ bytes, long long beg, long long e,
+                                                    const uint32_t *__restrict__ rpeq2, int m, int d) {
+    Myers q;
+    q.init(m);
+    const uint32_t top = 1u << (m - 1);
+    long long last = -1;
+    const long long avail = e - beg + 1;
+    const long long maxp = avail < (long long)m + d ? avail : (long long)m + d;
+    for (long long k = 0; k < maxp; ++k) {
+        q.step<true>(__ldg(rpeq2 + bytes[e - k]), top);
+        if (q.score == d) last = k;
+    }
+    return e - last;
+}
+
+__global__ void __launch_bounds__(ALN_THREADS) aln_pass2_kernel(const AlignParams p) {
+    __shared__ uint2 s_peq[256];
+    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) s_peq[i] = p.peq[i];
+    __syncthreads();
+    const int t = blockIdx.x * ALN_THREADS + threadIdx.x;
+    if (t >= p.n) return;
+    const int r = p.order[t];
+    const int nl = p.n_locs[r];
+    if (nl == 0) return;
+    const long long beg = p.off[r], end = p.off[r + 1];
+    const long long out0 = p.loc_off[r];
+    if ((unsigned long long)(out0 + nl) > p.loc_cap) return;      // the host grows the buffer and repeats the pass
+    const int m = p.m, d = p.dist[r];
+    const bool fwd = p.strand[r] == '+';
+    const uint32_t top = 1u << (m - 1);
+    Myers a;
+    a.init(m);
+    int k = 0;
+    for_each_byte(p.bytes, beg, end, [&](uint32_t ch, long long pos) {
+        const uint2 e = s_peq[ch];
+        a.step<false>(fwd ? e.x : e.y, top);
+        if (a.score == d && k < nl) {
+            // '+': end position (scTagger.py:185);  '-': start - len(seq) - 1 (scTagger.py:189)
+            const long long v = fwd ? (pos - beg) : (leftmost_start(p.bytes, beg, pos, p.rpeq2, m, d) - beg) - (end - beg) - 1;
+            p.locs[out0 + k] = (int)v;
+            ++k;
+        }
+    });
+}
+
+// ---- exclusive scan of n_locs (int32 -> int64 offsets, n + 1 entries) --------------------------------------------------
+__global__ void __launch_bounds__(1024) aln_block_sums_kernel(const int *__restrict__ n_locs, int n, long long *__restrict__ block_sums) {
+    __shared__ long long warp_sums[32];
+    const int i = blockIdx.x * 1024 + threadIdx.x;
+    long long v = i < n ? n_locs[i] : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, o);
+    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        long long w = warp_sums[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_down_sync(0xFFFFFFFFu, w, o);
+        if (threadIdx.x == 0) block_sums[blockIdx.x] = w;
+    }
+}
+
+// single block: exclusive prefix of the block sums in place, grand total to *total
+__global__ void __launch_bounds__(1024) aln_block_prefix_kernel(long long *__restrict__ block_sums, int n_blocks, long long *__restrict__ total) {
+    __shared__ long long sh[1024];
+    __shared__ long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n_blocks; base += 1024) {
+        const int i = base + threadIdx.x;
+        const long long v = i < n_blocks ? block_sums[i] : 0;
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {
+            const long long t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0;
+            __syncthreads();
+            sh[threadIdx.x] += t;
+            __syncthreads();
+        }
+        const long long incl = sh[threadIdx.x];
+        const long long c = carry;
+        if (i < n_blocks) block_sums[i] = c + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry;
+}
+
+__global__ void __launch_bounds__(1024) aln_scan_apply_kernel(const int *__restrict__ n_locs, int n,
+                                                              const long long *__restrict__ block_prefix,
+                                                              long long *__restrict__ loc_off) {
+    __shared__ long long warp_sums[32];
+    const int i = blockIdx.x * 1024 + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = i < n ? n_locs[i] : 0;
+    long long incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const long long v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        const long long w = warp_sums[lane];
+        long long wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long v = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        warp_sums[lane] = wi - w;
+    }
+    __syncthreads();
+    const long long excl = block_prefix[blockIdx.x] + warp_sums[warp] + incl - c;
+    if (i < n) {
+        loc_off[i] = excl;
+        if (i == n - 1) loc_off[n] = excl + c;
+    }
+}
+
+}  // namespace sct

@@ -1,0 +1,391 @@
+// Host side of the `extract_lr_bc` adapter alignment (C ABI: sct_align_* in include/sctagger_b200.h) around the kernels
+// of align_kernels.cuh.  Replaces get_lr_bc_alns / get_alns (reference scTagger.py:307-314, 176-196): instead of a
+// multiprocessing.Pool pickling every read to an edlib call, the reads are streamed through the GPU in byte-sized chunks
+// (pinned, double-buffered, one CUDA stream per buffer).  No CPU fallback.
+#include "align_kernels.cuh"
+#include "host_common.h"
+
+using namespace sct;
+using namespace scth;
+
+namespace {
+
+struct ASlot {
+    int64_t cap_reads = 0, cap_bytes = 0, cap_locs = 0;
+    uint8_t *h_bytes = nullptr;
+    long long *h_off = nullptr, *h_locoff = nullptr, *h_total = nullptr;
+    signed char *h_strand = nullptr;
+    int *h_dist = nullptr, *h_locs = nullptr;
+    uint8_t *d_bytes = nullptr;
+    long long *d_off = nullptr, *d_locoff = nullptr, *d_bsums = nullptr, *d_total = nullptr;
+    unsigned int *d_hist = nullptr;
+    int *d_order = nullptr, *d_dist = nullptr, *d_nlocs = nullptr, *d_locs = nullptr;
+    signed char *d_strand = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
+    int64_t n = 0, nbytes = 0, first = 0;
+    bool busy = false;
+};
+
+}  // namespace
+
+struct sct_align_handle {
+    int device = 0, m = 0, host_threads = 1;
+    uint2 *d_peq = nullptr;
+    uint32_t *d_rpeq2 = nullptr;
+    int64_t chunk_bytes = 0, chunk_reads = 0;
+    HostPool *pool = nullptr;
+    ASlot slot[2];
+    std::vector<int32_t> locs_host;
+    int64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool staged = false;
+};
+
+namespace {
+
+void free_aslot(ASlot &s) {
+    host_free(s.h_bytes); host_free(s.h_off); host_free(s.h_locoff); host_free(s.h_total); host_free(s.h_strand);
+    host_free(s.h_dist); host_free(s.h_locs);
+    dev_free(s.d_bytes); dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_bsums); dev_free(s.d_total);
+    dev_free(s.d_hist); dev_free(s.d_order); dev_free(s.d_dist); dev_free(s.d_nlocs); dev_free(s.d_locs);
+    dev_free(s.d_strand);
+    s.cap_reads = s.cap_bytes = s.cap_locs = 0;
+}
+
+int ensure_locs(ASlot &s, int64_t want) {
+    if (want <= s.cap_locs) return SCT_OK;
+    const int64_t c = std::max<int64_t>(want + want / 4, 4096);
+    host_free(s.h_locs);
+    dev_free(s.d_locs);
+    s.cap_locs = 0;
+    CUDA_TRY(cudaMalloc(&s.d_locs, (size_t)c * sizeof(int)));
+    CUDA_TRY(cudaMallocHost(&s.h_locs, (size_t)c * sizeof(int)));
+    s.cap_locs = c;
+    return SCT_OK;
+}
+
+int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes) {
+    if (!s.stream) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreate(&s.ev0));
+        CUDA_TRY(cudaEventCreate(&s.ev1));
+        CUDA_TRY(cudaEventCreate(&s.ev2));
+        CUDA_TRY(cudaEventCreate(&s.ev3));
+        CUDA_TRY(cudaMallocHost(&s.h_total, sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_total, sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_hist, ALN_BUCKETS * sizeof(unsigned int)));
+    }
+    if (reads > s.cap_reads) {
+        const int64_t c = std::max<int64_t>(reads, 1024);
+        host_free(s.h_off); host_free(s.h_locoff); host_free(s.h_strand); host_free(s.h_dist);
+        dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_bsums); dev_free(s.d_order); dev_free(s.d_dist);
+        dev_free(s.d_nlocs); dev_free(s.d_strand);
+        s.cap_reads = 0;
+        CUDA_TRY(cudaMallocHost(&s.h_off, (size_t)(c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMallocHost(&s.h_locoff, (size_t)(c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMallocHost(&s.h_strand, (size_t)c));
+        CUDA_TRY(cudaMallocHost(&s.h_dist, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_off, (size_t)(c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_locoff, (size_t)(c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_bsums, (size_t)((c + 1023) / 1024 + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_order, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_dist, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_nlocs, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_strand, (size_t)c));
+        s.cap_reads = c;
+        TRY(ensure_locs(s, c * 2));
+    }
+    if (bytes > s.cap_bytes) {
+        const int64_t c = std::max<int64_t>(bytes, 4096);
+        host_free(s.h_bytes);
+        dev_free(s.d_bytes);
+        s.cap_bytes = 0;
+        CUDA_TRY(cudaMallocHost(&s.h_bytes, (size_t)c + 64));
+        CUDA_TRY(cudaMalloc(&s.d_bytes, (size_t)c + 64));
+        s.cap_bytes = c;
+    }
+    return SCT_OK;
+}
+
+AlignParams make_aparams(sct_align_handle *h, ASlot &s) {
+    AlignParams p;
+    p.bytes = s.d_bytes;
+    p.off = s.d_off;
+    p.n = (int)s.n;
+    p.m = h->m;
+    p.peq = h->d_peq;
+    p.rpeq2 = h->d_rpeq2;
+    p.order = s.d_order;
+    p.strand = s.d_strand;
+    p.dist = s.d_dist;
+    p.n_locs = s.d_nlocs;
+    p.loc_off = s.d_locoff;
+    p.locs = s.d_locs;
+    p.loc_cap = (unsigned long long)s.cap_locs;
+    return p;
+}
+
+// length ordering, pass 1, scan; then the grand total and the fixed-size results start their way back
+int enqueue_pass1(sct_align_handle *h, ASlot &s) {
+    const int n = (int)s.n;
+    CUDA_TRY(cudaEventRecord(s.ev0, s.stream));
+    if (n > 0) {
+        const AlignParams p = make_aparams(h, s);
+        CUDA_TRY(cudaMemsetAsync(s.d_hist, 0, ALN_BUCKETS * sizeof(unsigned int), s.stream));
+        aln_hist_kernel<<<std::min((n + 255) / 256, 1184), 256, 0, s.stream>>>(s.d_off, n, s.d_hist);
+        aln_bucket_scan_kernel<<<1, ALN_BUCKETS, 0, s.stream>>>(s.d_hist);
+        aln_scatter_kernel<<<(n + 255) / 256, 256, 0, s.stream>>>(s.d_off, n, s.d_hist, s.d_order);
+        aln_pass1_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        const int nb = (n + 1023) / 1024;
+        aln_block_sums_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums);
+        aln_block_prefix_kernel<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total);
+        aln_scan_apply_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums, s.d_locoff);
+        CUDA_TRY(cudaGetLastError());
+        h->stats[0] += 7;
+    } else {
+        CUDA_TRY(cudaMemsetAsync(s.d_total, 0, sizeof(long long), s.stream));
+    }
+    CUDA_TRY(cudaEventRecord(s.ev1, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_total, s.d_total, sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    return SCT_OK;
+}
+
+int enqueue_fixed_copies(ASlot &s) {
+    const int64_t n = s.n;
+    if (n <= 0) return SCT_OK;
+    CUDA_TRY(cudaMemcpyAsync(s.h_strand, s.d_strand, (size_t)n, cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_dist, s.d_dist, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_locoff, s.d_locoff, (size_t)(n + 1) * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    return SCT_OK;
+}
+
+// after pass 1 has finished: size the location buffer, run pass 2
+int enqueue_pass2(sct_align_handle *h, ASlot &s, bool copy_back) {
+    const long long total = s.n > 0 ? *s.h_total : 0;
+    TRY(ensure_locs(s, total));
+    CUDA_TRY(cudaEventRecord(s.ev2, s.stream));
+    if (total > 0) {
+        const AlignParams p = make_aparams(h, s);
+        aln_pass2_kernel<<<((int)s.n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        CUDA_TRY(cudaGetLastError());
+        h->stats[0] += 1;
+        if (copy_back)
+            CUDA_TRY(cudaMemcpyAsync(s.h_locs, s.d_locs, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    }
+    CUDA_TRY(cudaEventRecord(s.ev3, s.stream));
+    return SCT_OK;
+}
+
+int stage_chunk(sct_align_handle *h, ASlot &s, const uint8_t *bytes, const int64_t *off, int64_t first, int64_t n) {
+    const int64_t b0 = off[first], nbytes = off[first + n] - b0;
+    if (nbytes < 0) return fail(SCT_E_ARG, "read_offsets must be non-decreasing (chunk starting at read %lld)", (long long)first);
+    TRY(ensure_aslot(s, n, nbytes));
+    if (nbytes > 0) par_memcpy(h->pool, s.h_bytes, bytes + b0, (size_t)nbytes);
+    std::atomic<bool> bad(false);
+    long long *dst = s.h_off;
+    const int64_t *src = off + first;
+    par_ranges(h->pool, n + 1, 1 << 16, [&](int64_t a, int64_t b) {
+        bool mine = false;
+        for (int64_t i = a; i < b; ++i) {
+            dst[i] = src[i] - b0;
+            if (i < n && src[i + 1] < src[i]) mine = true;
+        }
+        if (mine) bad = true;
+    });
+    if (bad) return fail(SCT_E_ARG, "read_offsets must be non-decreasing (chunk starting at read %lld)", (long long)first);
+    s.n = n;
+    s.nbytes = nbytes;
+    s.first = first;
+    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
+    h->stats[2] += nbytes + (n + 1) * (int64_t)sizeof(long long);
+    h->stats[1] += 1;
+    return SCT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sct_align_create(int device, const uint8_t *adapter, int32_t adapter_length, int32_t threads, double mem_gb,
+                     sct_align_handle **out) {
+    if (!out) return fail(SCT_E_ARG, "out is NULL");
+    *out = nullptr;
+    if (!adapter || adapter_length < 1) return fail(SCT_E_ARG, "adapter must not be empty");
+    if (adapter_length > 32) return fail(SCT_E_UNSUPPORTED, "adapter length %d > 32 is not implemented", adapter_length);
+    if (threads < 1) return fail(SCT_E_ARG, "threads must be >= 1 (scTagger.py:128)");
+    if (!(mem_gb > 0)) return fail(SCT_E_ARG, "mem must be > 0");
+    const int ndev = sct_device_count();
+    if (ndev == 0) return fail(SCT_E_CUDA, "no CUDA device available (sctagger_b200 has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(SCT_E_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    CUDA_TRY(cudaSetDevice(device));
+    sct_align_handle *h = new (std::nothrow) sct_align_handle();
+    if (!h) return fail(SCT_E_NOMEM, "out of host memory");
+    h->device = device;
+    h->m = adapter_length;
+    h->host_threads = std::max(1, std::min({(int)threads, 8, (int)std::thread::hardware_concurrency() / std::max(1, ndev)}));
+    h->pool = new (std::nothrow) HostPool(h->host_threads);
+    // a1 = adapter, a2 = rev_compl(a1) (scTagger.py:363-365; identity on non-ACGT, scTagger.py:146-155)
+    const int m = adapter_length;
+    std::vector<uint2> peq(256, make_uint2(0u, 0u));
+    std::vector<uint32_t> rpeq2(256, 0u);
+    for (int i = 0; i < m; ++i) {
+        const uint8_t c1 = adapter[i], c2 = comp_char(adapter[m - 1 - i]);
+        peq[c1].x |= 1u << i;
+        peq[c2].y |= 1u << i;
+        rpeq2[c2] |= 1u << (m - 1 - i);
+    }
+    CUDA_TRY(cudaMalloc(&h->d_peq, 256 * sizeof(uint2)));
+    CUDA_TRY(cudaMalloc(&h->d_rpeq2, 256 * sizeof(uint32_t)));
+    CUDA_TRY(cudaMemcpy(h->d_peq, peq.data(), 256 * sizeof(uint2), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(h->d_rpeq2, rpeq2.data(), 256 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    const double budget = mem_gb * (double)(1ull << 30);
+    h->chunk_bytes = (int64_t)std::min<double>(std::max<double>(budget / 8.0, 16.0 * (1 << 20)), 256.0 * (1 << 20));
+    h->chunk_reads = std::max<int64_t>(1024, h->chunk_bytes / 64);
+    *out = h;
+    return SCT_OK;
+}
+
+int sct_align_destroy(sct_align_handle *h) {
+    if (!h) return SCT_OK;
+    cudaSetDevice(h->device);
+    for (ASlot &s : h->slot) {
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        free_aslot(s);
+        if (s.ev0) cudaEventDestroy(s.ev0);
+        if (s.ev1) cudaEventDestroy(s.ev1);
+        if (s.ev2) cudaEventDestroy(s.ev2);
+        if (s.ev3) cudaEventDestroy(s.ev3);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    dev_free(h->d_peq);
+    dev_free(h->d_rpeq2);
+    delete h->pool;
+    delete h;
+    return SCT_OK;
+}
+
+int sct_align_set_option(sct_align_handle *h, const char *key, int64_t value) {
+    if (!h || !key) return fail(SCT_E_ARG, "NULL argument");
+    const std::string k(key);
+    if (k == "chunk_bytes") {
+        if (value < 1) return fail(SCT_E_ARG, "chunk_bytes must be >= 1");
+        h->chunk_bytes = value;
+    } else if (k == "chunk_reads") {
+        if (value < 1) return fail(SCT_E_ARG, "chunk_reads must be >= 1");
+        h->chunk_reads = value;
+    } else {
+        return fail(SCT_E_ARG, "unknown option '%s'", key);
+    }
+    return SCT_OK;
+}
+
+int sct_align_stats(sct_align_handle *h, int64_t stats[8]) {
+    if (!h || !stats) return fail(SCT_E_ARG, "NULL argument");
+    memcpy(stats, h->stats, sizeof h->stats);
+    return SCT_OK;
+}
+
+int sct_align(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *read_offsets, int64_t n, int8_t *strand,
+              int32_t *dist, int64_t *loc_offsets, const int32_t **locs, int64_t *n_locs) {
+    if (!h) return fail(SCT_E_ARG, "NULL handle");
+    if (n < 0) return fail(SCT_E_ARG, "n < 0");
+    if (!read_offsets || !loc_offsets || !locs || !n_locs || (n > 0 && (!strand || !dist))) return fail(SCT_E_ARG, "NULL argument");
+    if (n > 0 && !read_bytes && read_offsets[n] > read_offsets[0]) return fail(SCT_E_ARG, "read_bytes is NULL");
+    CUDA_TRY(cudaSetDevice(h->device));
+    memset(h->stats, 0, sizeof h->stats);
+    h->locs_host.clear();
+    h->staged = false;
+    int64_t loc_base = 0;
+
+    auto finish = [&](int si) -> int {
+        ASlot &s = h->slot[si];
+        if (!s.busy) return SCT_OK;
+        CUDA_TRY(cudaStreamSynchronize(s.stream));            // pass 1, total and the fixed-size results are back
+        TRY(enqueue_pass2(h, s, true));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        const int64_t cn = s.n;
+        const long long total = cn > 0 ? *s.h_total : 0;
+        float a = 0.f, b = 0.f;
+        cudaEventElapsedTime(&a, s.ev0, s.ev1);
+        cudaEventElapsedTime(&b, s.ev2, s.ev3);
+        h->stats[4] += (int64_t)((a + b) * 1e6);
+        h->stats[3] += cn * 13 + 8 + total * 4;
+        if (cn > 0) {
+            par_memcpy(h->pool, strand + s.first, s.h_strand, (size_t)cn);
+            par_memcpy(h->pool, dist + s.first, s.h_dist, (size_t)cn * sizeof(int));
+            int64_t *dst = loc_offsets + s.first;
+            const long long *src = s.h_locoff;
+            par_ranges(h->pool, cn, 1 << 16, [&](int64_t x, int64_t y) {
+                for (int64_t i = x; i < y; ++i) dst[i] = loc_base + src[i];
+            });
+            if (total > 0) {
+                const size_t at = h->locs_host.size();
+                h->locs_host.resize(at + (size_t)total);
+                par_memcpy(h->pool, h->locs_host.data() + at, s.h_locs, (size_t)total * sizeof(int));
+            }
+        }
+        loc_base += total;
+        s.busy = false;
+        return SCT_OK;
+    };
+
+    int64_t first = 0, chunk = 0;
+    while (first < n) {
+        int64_t cn = std::min<int64_t>(h->chunk_reads, n - first);
+        const int64_t limit = read_offsets[first] + h->chunk_bytes;
+        if (read_offsets[first + cn] > limit) {
+            const int64_t *e = std::upper_bound(read_offsets + first, read_offsets + first + cn + 1, limit);
+            cn = std::max<int64_t>(1, (e - (read_offsets + first)) - 1);
+        }
+        const int si = (int)(chunk & 1);
+        TRY(finish(si));
+        ASlot &s = h->slot[si];
+        TRY(stage_chunk(h, s, read_bytes, read_offsets, first, cn));
+        TRY(enqueue_pass1(h, s));
+        TRY(enqueue_fixed_copies(s));
+        s.busy = true;
+        first += cn;
+        ++chunk;
+    }
+    // drain in chunk order: the slot holding the older chunk first
+    const int older = (int)(chunk & 1);
+    TRY(finish(older));
+    TRY(finish(1 - older));
+    loc_offsets[n] = loc_base;
+    *locs = h->locs_host.empty() ? nullptr : h->locs_host.data();
+    *n_locs = loc_base;
+    h->stats[5] = n;
+    return SCT_OK;
+}
+
+int sct_align_stage(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *read_offsets, int64_t n) {
+    if (!h || !read_offsets || n < 0) return fail(SCT_E_ARG, "bad argument");
+    CUDA_TRY(cudaSetDevice(h->device));
+    ASlot &s = h->slot[0];
+    memset(h->stats, 0, sizeof h->stats);
+    TRY(stage_chunk(h, s, read_bytes, read_offsets, 0, n));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    h->staged = true;
+    return SCT_OK;
+}
+
+int sct_align_run_staged(sct_align_handle *h, float *pass_ms, float *pass1_kernel_ms) {
+    if (!h) return fail(SCT_E_ARG, "NULL handle");
+    if (!h->staged) return fail(SCT_E_STATE, "sct_align_stage has not been called");
+    CUDA_TRY(cudaSetDevice(h->device));
+    ASlot &s = h->slot[0];
+    h->stats[0] = 0;
+    TRY(enqueue_pass1(h, s));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    TRY(enqueue_pass2(h, s, false));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    float a = 0.f, b = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&a, s.ev0, s.ev1));
+    CUDA_TRY(cudaEventElapsedTime(&b, s.ev2, s.ev3));
+    if (pass_ms) *pass_ms = a + b;
+    if (pass1_kernel_ms) *pass1_kernel_ms = a;
+    return SCT_OK;
+}
+
+}  // extern "C"

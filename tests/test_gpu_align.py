@@ -1,0 +1,84 @@
+"""GPU parity of the extract_lr_bc adapter alignment (sct_align, through the C ABI) against the CPU oracle
+(oracle/align_oracle.c, edlib HW semantics restated — parity with edlib itself is unpinned).  Bit-exact: integer work."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from sctagger_b200 import _lib, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _pack(reads):
+    off = np.zeros(len(reads) + 1, np.int64)
+    np.cumsum([len(r) for r in reads], out=off[1:])
+    return np.frombuffer(b"".join(reads), np.uint8), off
+
+
+def _same(got, want):
+    for g, w, name in zip(got, want, ("strand", "dist", "loc_offsets", "locs")):
+        assert np.array_equal(g, w), name
+
+
+def test_hand_cases_and_edges():
+    a1 = b"ACGTT"
+    reads = [b"GGACGTTGG", b"GGAACGTGG", b"", b"GGGGGG", b"ACGTTACGTT", b"TTACGTCC", b"A", b"ACG", b"N", b"acgtt",
+             b"ACGTNACGTT" * 30, b"AACGT" * 50, b"T" * 17, b"AACGTACGTT"]
+    rb, off = _pack(reads)
+    _same(_lib.align_reads(a1, rb, off), oracle.align(a1, rb, off))
+    # n = 0
+    s, d, lo, locs = _lib.align_reads(a1, np.zeros(0, np.uint8), np.zeros(1, np.int64))
+    assert s.size == 0 and lo.tolist() == [0] and locs.size == 0
+
+
+@pytest.mark.parametrize("seed,adapter", [(1, synth.ADAPTER), (2, b"ACGTACGTAC"), (3, b"GATTACAGATTACAGATTACAGATTACAGATT"),
+                                          (4, b"ANCGT"), (5, b"T"), (6, b"CTACACGACGCTCTTCCGATCTA")])
+def test_random_reads_vs_oracle(seed, adapter):
+    rb, off = synth.make_reads(3000, seed, adapter=adapter if (b"N" not in adapter and len(adapter) > 4) else synth.ADAPTER,
+                               median_len=300, min_len=1, max_len=1500)
+    rb = rb.copy()
+    rng = np.random.default_rng(seed)
+    rb[rng.integers(0, rb.size, size=500)] = ord("N")
+    rb[rng.integers(0, rb.size, size=500)] = ord("a")
+    want = oracle.align(adapter, rb, off)
+    _same(_lib.align_reads(adapter, rb, off), want)
+    # ragged chunking: by bytes and by reads
+    _same(_lib.align_reads(adapter, rb, off, chunk_bytes=5000), want)
+    _same(_lib.align_reads(adapter, rb, off, chunk_reads=7, chunk_bytes=1 << 20), want)
+
+
+def test_cfg5_shape_sample_and_staged_timing():
+    """BASELINE config 5 shape (log-normal lengths, median 900, 22-nt adapter) on a sample the DP oracle finishes fast."""
+    rb, off = synth.make_reads(20_000, synth.SEEDS["cfg5"])
+    want = oracle.align(synth.ADAPTER, rb, off, algo="bv")
+    with _lib.Aligner(synth.ADAPTER, threads=8) as a:
+        _same(a.align(rb, off), want)
+        st = a.stats()
+        assert st["reads"] == 20_000 and st["launches"] >= 8 and st["h2d_bytes"] >= rb.size
+        a.stage(rb, off)
+        ms, k1 = a.run_staged()
+        assert ms > 0 and 0 < k1 <= ms
+
+
+def test_long_reads_and_length_sorting():
+    rng = np.random.default_rng(3)
+    lens = [0, 1, 15, 16, 17, 31, 32, 33, 40_000, 100_000, 5, 70_000]
+    reads = [bytes(synth.ACGT[rng.integers(0, 4, size=n)]) for n in lens]
+    reads[8] = reads[8][:20_000] + synth.ADAPTER + reads[8][20_022:]
+    rb, off = _pack(reads)
+    _same(_lib.align_reads(synth.ADAPTER, rb, off), oracle.align(synth.ADAPTER, rb, off, algo="bv"))
+
+
+def test_align_errors():
+    with pytest.raises(_lib.SctError) as e:
+        _lib.Aligner(b"A" * 33)
+    assert e.value.code == -4
+    with pytest.raises(_lib.SctError):
+        _lib.Aligner(b"")
+    with pytest.raises(_lib.SctError):
+        _lib.Aligner(synth.ADAPTER, threads=0)
+    with _lib.Aligner(synth.ADAPTER) as a:
+        with pytest.raises(_lib.SctError):
+            a.align(np.zeros(4, np.uint8), np.array([0, 3, 2], np.int64))
+        with pytest.raises(_lib.SctError):
+            a.run_staged()
