@@ -7,7 +7,8 @@ Same flags, defaults and assertions as the reference.  Differences a user can se
   * `-p` is accepted and ignored — exactly what the reference's match_trie does (show_plot_match_trie is never called).
   * `--gpus N` / `--devices 0,1,..` (new, optional) shard the reads over several GPUs of this box.
   * log lines go to STDERR, so that without `-o` STDOUT holds the TSV rows only (the reference interleaves both).
-Only the sub-command this package replaces is accepted; the other stages stay with the reference.
+`extract_lr_bc` (reference scTagger.py:25-49, 100-128) is accepted with its own flags as well: its adapter alignment runs
+on the GPU (`-p` plotting is not part of this path and is ignored).  The other stages stay with the reference.
 """
 from __future__ import annotations
 
@@ -35,26 +36,60 @@ def build_parser() -> argparse.ArgumentParser:
                    help="Path to output file. Output file is gzipped. STDOUT is in normal text. Default: stdout")
     p.add_argument("--gpus", type=int, default=None, help="Number of GPUs to shard the reads over. Default: 1")
     p.add_argument("--devices", type=str, default=None, help="Comma separated CUDA device indices (overrides --gpus)")
+    q = subparsers.add_parser("extract_lr_bc")          # scTagger.py:25-49
+    q.add_argument("-r", "--reads", nargs="+", type=str, required=True, help="Space separated paths to reads in FASTQ")
+    q.add_argument("-g", "--ranges", nargs="+", type=str, default=list(),
+                   help="Space separated ranges of where the SR adapter should be found on the LRs, e.g. f20:40 r1:30 "
+                        "(1-indexed, inclusive; f = from the start on the forward strand, r = from the end on the "
+                        "reverse strand). Default: Detect from data.")
+    q.add_argument("-z", "--gzipped", dest="gzipped", action="store_true",
+                   help="Indicate input is gzipped. Default: Assume input is gzipped if it ends with \".gz\".")
+    q.add_argument("-t", "--threads", default=1, type=int, help="Number of threads. Default: 1")
+    q.add_argument("-sa", "--short-read-adapter", type=str, default="CTACACGACGCTCTTCCGATCT",
+                   help="Short-read adapter. Default: CTACACGACGCTCTTCCGATCT")
+    q.add_argument("-o", "--outfile", type=str, default=None,
+                   help="Path to output file. Output file is gzipped. STDOUT is in normal text. Default: stdout")
+    q.add_argument("-p", "--plotfile", type=str, default=None, help="Path to plot file. Default: no plotting")
+    q.add_argument("--num-bp-after", type=int, default=20,
+                   help="Number of bases after the end of the SR adapter alignment to generate. Default: 20")
+    q.add_argument("--gpus", type=int, default=None, help="Number of GPUs to shard the reads over. Default: 1")
+    q.add_argument("--devices", type=str, default=None, help="Comma separated CUDA device indices (overrides --gpus)")
     return parser
+
+
+def _devices(args):
+    if args.devices is not None:
+        args.devices = [int(x) for x in args.devices.split(",") if x != ""]
+    elif args.gpus is not None:
+        assert args.gpus >= 1
+        args.devices = list(range(args.gpus))
 
 
 def parse_args(argv=None):
     args = build_parser().parse_args(argv)
+    if args.subcommand == "extract_lr_bc":   # scTagger.py:100-128
+        from .extract_lr_bc import parse_ranges_flag
+        assert 0 < args.num_bp_after
+        args.ranges = parse_ranges_flag(args.ranges)
+        assert args.threads > 0
+        _devices(args)
     if args.subcommand == "match_trie":      # scTagger.py:140-143
         assert args.mem > 0
         assert args.barcode_length > 0
         assert args.barcode_length > args.max_error >= 0
-        if args.devices is not None:
-            args.devices = [int(x) for x in args.devices.split(",") if x != ""]
-        elif args.gpus is not None:
-            assert args.gpus >= 1
-            args.devices = list(range(args.gpus))
+        _devices(args)
     return args
 
 
 def main(argv=None):
     from . import match_trie as mt
     args = parse_args(argv)
+    if args.subcommand == "extract_lr_bc":
+        # the reference logs this stage to STDERR already (scTagger.py:163, 213, 249, ...); only the Namespace goes to STDOUT
+        from . import extract_lr_bc as lr
+        print(args, file=sys.stderr)
+        lr.extract_lr_bc(args)
+        return 0
     # the reference prints the Namespace and its progress lines to STDOUT (scTagger.py:849, 604, 628, ...);
     # here they go to STDERR so that STDOUT output stays a clean TSV
     with contextlib.redirect_stdout(sys.stderr):
