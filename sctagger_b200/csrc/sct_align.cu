@@ -240,7 +240,9 @@ int sct_align_create(int device, const uint8_t *adapter, int32_t adapter_length,
     CUDA_TRY(cudaMemcpy(h->d_peq, peq.data(), 256 * sizeof(uint2), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(h->d_rpeq2, rpeq2.data(), 256 * sizeof(uint32_t), cudaMemcpyHostToDevice));
     const double budget = mem_gb * (double)(1ull << 30);
-    h->chunk_bytes = (int64_t)std::min<double>(std::max<double>(budget / 8.0, 16.0 * (1 << 20)), 256.0 * (1 << 20));
+    // 128 MiB chunks: one thread walks one read, so a pass cannot be shorter than its longest read (~0.3 ms for 5 kb);
+    // smaller chunks pay that floor too often, one single chunk would not overlap staging / copies with the kernels
+    h->chunk_bytes = (int64_t)std::min<double>(std::max<double>(budget / 8.0, 16.0 * (1 << 20)), 128.0 * (1 << 20));
     h->chunk_reads = std::max<int64_t>(1024, h->chunk_bytes / 64);
     *out = h;
     return SCT_OK;
