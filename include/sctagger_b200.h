@@ -34,6 +34,8 @@ extern "C" {
 #define SCT_E_NOMEM      -3   /* host or device allocation failed */
 #define SCT_E_UNSUPPORTED -4  /* parameter combination outside the implemented range (see sct_create) */
 #define SCT_E_STATE      -5   /* call sequence error (e.g. results requested before a run) */
+#define SCT_E_IO         -6   /* file cannot be opened / read / decompressed (the reference would raise OSError) */
+#define SCT_E_FORMAT     -7   /* malformed input row (the reference would raise IndexError, scTagger.py:613-614) */
 
 typedef struct sct_handle sct_handle;
 
@@ -147,6 +149,42 @@ int sct_align_run_staged(sct_align_handle *h, float *pass_ms, float *pass1_kerne
  * [5] reads, [6..7] reserved.   Options: "chunk_bytes", "chunk_reads". */
 int sct_align_stats(sct_align_handle *h, int64_t stats[8]);
 int sct_align_set_option(sct_align_handle *h, const char *key, int64_t value);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Native host I/O of the formats either side of the kernels (§8(f) rank 2).  Host code only
+ * (threads + zlib); no GPU is needed and nothing here computes a match.
+ *
+ *   sct_io_read_long_reads  <- read_long_reads (scTagger.py:602-628): TSV, gzip iff the name ends with ".gz"; per line
+ *        column 0 = read name, column 3 = segment (may be empty); a row with fewer than four columns -> SCT_E_FORMAT
+ *        (the reference's IndexError).  -> names and segments as concatenated bytes + n+1 offsets, library-owned.
+ *   sct_io_read_fastqs      <- read_fastqs (scTagger.py:159-173), one file per call: gzip iff `gzipped` or ".gz"; line 0
+ *        of every record: name = first whitespace-separated token minus its first character; line 1: the sequence with
+ *        trailing whitespace stripped.
+ *   sct_io_format_matches   <- the writer of match_trie (scTagger.py:777-789): one row `name \t e \t n_ties \t segment \t
+ *        b1,b2,...` per read with min_ed >= 0, in read order; tie ids as sct_match returns them (forward barcode for
+ *        strand 1, its reverse complement for strand 0).  gzip_level 0 = plain text, 1..9 = gzip (one member per block
+ *        of rows, compressed in parallel; decompresses to the same bytes as the reference's single member).
+ *   sct_io_format_lr_bc     <- output_matches of extract_lr_bc (scTagger.py:317-320): `rname \t dist \t loc \t
+ *        seq[s:e or None]` for every read; dist < 0 = rejected by filter_aln: `-1`, `NA`, empty sequence.
+ *   The buffers stay valid until the matching *_free call.
+ */
+typedef struct sct_reads sct_reads;
+typedef struct sct_buffer sct_buffer;
+int sct_io_read_long_reads(const char *path, int32_t threads, sct_reads **out);
+int sct_io_read_fastqs(const char *path, int32_t gzipped, int32_t threads, sct_reads **out);
+int sct_io_reads_info(sct_reads *r, int64_t *n, const uint8_t **name_bytes, const int64_t **name_offsets,
+                      const uint8_t **seg_bytes, const int64_t **seg_offsets);
+int sct_io_reads_free(sct_reads *r);
+int sct_io_format_matches(const uint8_t *name_bytes, const int64_t *name_offsets, const uint8_t *seg_bytes,
+                          const int64_t *seg_offsets, int64_t n, const int32_t *min_ed, const int32_t *n_ties,
+                          const int64_t *tie_offsets, const int32_t *tie_ids, const uint8_t *barcodes,
+                          int32_t n_barcodes, int32_t barcode_length, int32_t gzip_level, int32_t threads,
+                          sct_buffer **out);
+int sct_io_format_lr_bc(const uint8_t *name_bytes, const int64_t *name_offsets, const uint8_t *read_bytes,
+                        const int64_t *read_offsets, int64_t n, const int64_t *dist, const int64_t *loc,
+                        const int64_t *s, const int64_t *e, int32_t gzip_level, int32_t threads, sct_buffer **out);
+int sct_io_buffer_info(sct_buffer *b, const uint8_t **data, int64_t *size, int64_t *rows);
+int sct_io_buffer_free(sct_buffer *b);
 
 #ifdef __cplusplus
 }

@@ -21,6 +21,8 @@ EXPORTS = (
     "sct_measure_int32_peak", "sct_flush_l2",
     "sct_align_create", "sct_align_destroy", "sct_align", "sct_align_stage", "sct_align_run_staged",
     "sct_align_stats", "sct_align_set_option",
+    "sct_io_read_long_reads", "sct_io_read_fastqs", "sct_io_reads_info", "sct_io_reads_free",
+    "sct_io_format_matches", "sct_io_format_lr_bc", "sct_io_buffer_info", "sct_io_buffer_free",
 )
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
@@ -93,13 +95,41 @@ def lib():
             L.sct_align_stats.argtypes = [_vp, _i64p]
             L.sct_align_set_option.restype = ctypes.c_int
             L.sct_align_set_option.argtypes = [_vp, ctypes.c_char_p, ctypes.c_int64]
+            L.sct_io_read_long_reads.restype = ctypes.c_int
+            L.sct_io_read_long_reads.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.POINTER(_vp)]
+            L.sct_io_read_fastqs.restype = ctypes.c_int
+            L.sct_io_read_fastqs.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(_vp)]
+            L.sct_io_reads_info.restype = ctypes.c_int
+            L.sct_io_reads_info.argtypes = [_vp, _i64p, ctypes.POINTER(_u8p), ctypes.POINTER(_i64p),
+                                            ctypes.POINTER(_u8p), ctypes.POINTER(_i64p)]
+            L.sct_io_reads_free.restype = ctypes.c_int
+            L.sct_io_reads_free.argtypes = [_vp]
+            L.sct_io_format_matches.restype = ctypes.c_int
+            L.sct_io_format_matches.argtypes = [_u8p, _i64p, _u8p, _i64p, ctypes.c_int64, _i32p, _i32p, _i64p, _i32p,
+                                                _u8p, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                                ctypes.POINTER(_vp)]
+            L.sct_io_format_lr_bc.restype = ctypes.c_int
+            L.sct_io_format_lr_bc.argtypes = [_u8p, _i64p, _u8p, _i64p, ctypes.c_int64, _i64p, _i64p, _i64p, _i64p,
+                                              ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(_vp)]
+            L.sct_io_buffer_info.restype = ctypes.c_int
+            L.sct_io_buffer_info.argtypes = [_vp, ctypes.POINTER(_u8p), _i64p, _i64p]
+            L.sct_io_buffer_free.restype = ctypes.c_int
+            L.sct_io_buffer_free.argtypes = [_vp]
             _lib = L
     return _lib
 
 
+E_IO, E_FORMAT = -6, -7
+
+
 def _check(rc):
     if rc != 0:
-        raise SctError(rc, lib().sct_last_error().decode("utf-8", "replace"))
+        msg = lib().sct_last_error().decode("utf-8", "replace")
+        if rc == E_FORMAT:          # the reference's IndexError on a short row (scTagger.py:613-614)
+            raise IndexError(msg)
+        if rc == E_IO:              # the reference's open()/gzip.open() failures
+            raise OSError(msg)
+        raise SctError(rc, msg)
 
 
 def device_count() -> int:
@@ -385,3 +415,100 @@ def match_segments(barcodes: np.ndarray, seg_bytes: np.ndarray, offsets: np.ndar
     if errors:
         raise errors[0]
     return concat_results(results)
+
+
+# ---- native host I/O (sct_io_*): parse / format / gzip with the host threads, no GPU involved ---------------------------
+def host_threads(threads=None) -> int:
+    n = os.cpu_count() or 1
+    return max(1, min(int(threads) if threads else n, n, 64))
+
+
+def _take_reads(h):
+    """Copy the four arrays out of a sct_reads handle and free it -> (name_bytes, name_offsets, seg_bytes, seg_offsets)."""
+    try:
+        n = ctypes.c_int64(0)
+        nb, sb = _u8p(), _u8p()
+        no, so = _i64p(), _i64p()
+        _check(lib().sct_io_reads_info(h, ctypes.byref(n), ctypes.byref(nb), ctypes.byref(no), ctypes.byref(sb),
+                                       ctypes.byref(so)))
+        n = int(n.value)
+        name_off = np.ctypeslib.as_array(no, shape=(n + 1,)).copy()
+        seg_off = np.ctypeslib.as_array(so, shape=(n + 1,)).copy()
+        nbytes, sbytes = int(name_off[n]), int(seg_off[n])
+        name_bytes = np.ctypeslib.as_array(nb, shape=(nbytes,)).copy() if nbytes else np.zeros(0, dtype=np.uint8)
+        seg_bytes = np.ctypeslib.as_array(sb, shape=(sbytes,)).copy() if sbytes else np.zeros(0, dtype=np.uint8)
+        return name_bytes, name_off, seg_bytes, seg_off
+    finally:
+        lib().sct_io_reads_free(h)
+
+
+def io_read_long_reads(path: str, threads=None):
+    """sct_io_read_long_reads -> (name_bytes u8, name_offsets i64[n+1], seg_bytes u8, seg_offsets i64[n+1])."""
+    h = _vp()
+    _check(lib().sct_io_read_long_reads(os.fsencode(path), host_threads(threads), ctypes.byref(h)))
+    return _take_reads(h)
+
+
+def io_read_fastqs(path: str, gzipped: bool = False, threads=None):
+    """sct_io_read_fastqs, one file -> (name_bytes, name_offsets, read_bytes, read_offsets)."""
+    h = _vp()
+    _check(lib().sct_io_read_fastqs(os.fsencode(path), 1 if gzipped else 0, host_threads(threads), ctypes.byref(h)))
+    return _take_reads(h)
+
+
+def _take_buffer(h):
+    try:
+        data = _u8p()
+        size, rows = ctypes.c_int64(0), ctypes.c_int64(0)
+        _check(lib().sct_io_buffer_info(h, ctypes.byref(data), ctypes.byref(size), ctypes.byref(rows)))
+        return (ctypes.string_at(data, int(size.value)) if size.value else b""), int(rows.value)
+    finally:
+        lib().sct_io_buffer_free(h)
+
+
+def _i64(a):
+    a = np.ascontiguousarray(a, dtype=np.int64)
+    return a if a.size else np.zeros(1, dtype=np.int64)
+
+
+def _i32(a):
+    a = np.ascontiguousarray(a, dtype=np.int32)
+    return a if a.size else np.zeros(1, dtype=np.int32)
+
+
+def io_format_matches(name_bytes, name_offsets, seg_bytes, seg_offsets, result, barcode_matrix, gzip_level=0,
+                      threads=None):
+    """sct_io_format_matches -> (bytes of the TSV rows, gzip members when gzip_level > 0; number of rows)."""
+    bm = np.ascontiguousarray(barcode_matrix, dtype=np.uint8)
+    n = int(np.asarray(seg_offsets).shape[0]) - 1
+    nb, no, sb, so = _as_u8(name_bytes), _i64(name_offsets), _as_u8(seg_bytes), _i64(seg_offsets)
+    me, nt, to, ti = _i32(result.min_ed), _i32(result.n_ties), _i64(result.tie_offsets), _i32(result.tie_ids)
+    h = _vp()
+    _check(lib().sct_io_format_matches(_ptr(nb, ctypes.c_uint8), _ptr(no, ctypes.c_int64), _ptr(sb, ctypes.c_uint8),
+                                       _ptr(so, ctypes.c_int64), n, _ptr(me, ctypes.c_int32), _ptr(nt, ctypes.c_int32),
+                                       _ptr(to, ctypes.c_int64), _ptr(ti, ctypes.c_int32),
+                                       _ptr(_as_u8(bm), ctypes.c_uint8), int(bm.shape[0]), int(bm.shape[1]),
+                                       int(gzip_level), host_threads(threads), ctypes.byref(h)))
+    return _take_buffer(h)
+
+
+def io_format_lr_bc(name_bytes, name_offsets, read_bytes, read_offsets, dist, loc, s, e, gzip_level=0, threads=None):
+    """sct_io_format_lr_bc -> (bytes, rows)."""
+    n = int(np.asarray(read_offsets).shape[0]) - 1
+    nb, no, rb, ro = _as_u8(name_bytes), _i64(name_offsets), _as_u8(read_bytes), _i64(read_offsets)
+    d, l, s_, e_ = _i64(dist), _i64(loc), _i64(s), _i64(e)
+    h = _vp()
+    _check(lib().sct_io_format_lr_bc(_ptr(nb, ctypes.c_uint8), _ptr(no, ctypes.c_int64), _ptr(rb, ctypes.c_uint8),
+                                     _ptr(ro, ctypes.c_int64), n, _ptr(d, ctypes.c_int64), _ptr(l, ctypes.c_int64),
+                                     _ptr(s_, ctypes.c_int64), _ptr(e_, ctypes.c_int64), int(gzip_level),
+                                     host_threads(threads), ctypes.byref(h)))
+    return _take_buffer(h)
+
+
+def pack_names(names):
+    """list of str/bytes -> (name_bytes u8, name_offsets i64[n+1])."""
+    enc = [x.encode("latin-1") if isinstance(x, str) else bytes(x) for x in names]
+    off = np.zeros(len(enc) + 1, dtype=np.int64)
+    if enc:
+        np.cumsum(np.fromiter((len(x) for x in enc), dtype=np.int64, count=len(enc)), out=off[1:])
+    return np.frombuffer(b"".join(enc), dtype=np.uint8), off

@@ -92,11 +92,15 @@ def main(argv=None):
         return 0
     # the reference prints the Namespace and its progress lines to STDOUT (scTagger.py:849, 604, 628, ...);
     # here they go to STDERR so that STDOUT output stays a clean TSV
+    if args.outfile:
+        with contextlib.redirect_stdout(sys.stderr):
+            print(args)
+            mt.match_trie(args)
+        return 0
     with contextlib.redirect_stdout(sys.stderr):
         print(args)
-        if args.subcommand == "match_trie":
-            data = mt.match_trie_bytes(args)
-    mt.write_matches(args.outfile, data)
+        data = mt.match_trie_bytes(args)
+    mt.write_matches(None, data)
     return 0
 
 

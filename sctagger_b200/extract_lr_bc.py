@@ -16,26 +16,31 @@ alignments as arrays (`Alignments`) instead of a list of tuples; `Alignments.tup
 """
 from __future__ import annotations
 
-import gzip
 import sys
 from collections import deque
 from dataclasses import dataclass
 
 import numpy as np
 
-from .match_trie import rev_compl
+from .match_trie import GZIP_LEVEL, rev_compl
 
 DEFAULT_ADAPTER = "CTACACGACGCTCTTCCGATCT"      # scTagger.py:42
 
 
 @dataclass
 class Reads:
-    names: list            # rnames (bytes)
-    read_bytes: np.ndarray  # uint8, all sequences concatenated
-    offsets: np.ndarray    # int64[n+1]
+    name_bytes: np.ndarray    # uint8, all rnames concatenated
+    name_offsets: np.ndarray  # int64[n+1]
+    read_bytes: np.ndarray    # uint8, all sequences concatenated
+    offsets: np.ndarray       # int64[n+1]
 
     def __len__(self):
-        return len(self.names)
+        return int(self.offsets.shape[0]) - 1
+
+    @property
+    def names(self):
+        raw, o = self.name_bytes.tobytes(), self.name_offsets.tolist()
+        return [raw[o[i]:o[i + 1]] for i in range(len(self))]
 
     def seq(self, i: int) -> bytes:
         return self.read_bytes[self.offsets[i]:self.offsets[i + 1]].tobytes()
@@ -64,29 +69,30 @@ class Alignments:
         return out
 
 
-def read_fastqs(fastqs, gzipped=False) -> Reads:
+def read_fastqs(fastqs, gzipped=False, threads=None) -> Reads:
     """Line 0 of every record: name = first whitespace-separated token minus its first character; line 1: the sequence
-    with trailing whitespace stripped (scTagger.py:159-173).  gzip iff `gzipped` or the name ends with '.gz'."""
-    names, seqs = [], []
+    with trailing whitespace stripped (scTagger.py:159-173).  gzip iff `gzipped` or the name ends with '.gz'.  Parsed
+    natively (sct_io_read_fastqs), one file at a time, concatenated in argument order."""
+    from . import _lib
+    parts = []
     for fastq in fastqs:
         print(f"Reading {fastq}", file=sys.stderr)
-        if gzipped or fastq.endswith(".gz"):
-            with gzip.open(fastq, "rb") as f:
-                data = f.read()
-        else:
-            with open(fastq, "rb") as f:
-                data = f.read()
-        lines = data.split(b"\n")
-        if lines and lines[-1] == b"":
-            lines.pop()
-        for l in lines[0::4]:
-            names.append(l.split()[0][1:])
-        for l in lines[1::4]:
-            seqs.append(l.rstrip())
-    offsets = np.zeros(len(seqs) + 1, dtype=np.int64)
-    if seqs:
-        np.cumsum(np.fromiter((len(s) for s in seqs), dtype=np.int64, count=len(seqs)), out=offsets[1:])
-    return Reads(names, np.frombuffer(b"".join(seqs), dtype=np.uint8), offsets)
+        parts.append(_lib.io_read_fastqs(fastq, bool(gzipped), threads))
+    if len(parts) == 1:
+        return Reads(*parts[0])
+    if not parts:
+        z8, z64 = np.zeros(0, dtype=np.uint8), np.zeros(1, dtype=np.int64)
+        return Reads(z8, z64, z8, z64.copy())
+
+    def cat_off(k):
+        out, base = [], 0
+        for p in parts:
+            out.append(p[k][:-1] + base)
+            base += int(p[k][-1])
+        out.append(np.array([base], dtype=np.int64))
+        return np.concatenate(out)
+
+    return Reads(np.concatenate([p[0] for p in parts]), cat_off(1), np.concatenate([p[2] for p in parts]), cat_off(3))
 
 
 def get_lr_bc_alns(reads: Reads, threads: int, adapter: str = DEFAULT_ADAPTER, mem_gb: float = 16.0,
@@ -227,40 +233,30 @@ def get_filter_alns(alns: Alignments, range_dicts: RangeDicts, num_bp_after: int
     return dist, loc, s, e
 
 
-def format_rows(reads: Reads, filtered) -> bytes:
-    """`rname \\t dist \\t loc \\t seq[s:e or None]` per read (scTagger.py:317-320), loc = 'NA' for filtered reads."""
+def format_rows(reads: Reads, filtered, gzip_level: int = 0, threads=None) -> bytes:
+    """`rname \\t dist \\t loc \\t seq[s:e or None]` per read (scTagger.py:317-320), loc = 'NA' for filtered reads.
+    Formatted natively (sct_io_format_lr_bc); gzip_level > 0 returns the rows as gzip members."""
+    from . import _lib
     dist, loc, s, e = filtered
-    raw = reads.read_bytes.tobytes()
-    off = reads.offsets
-    out = []
-    for i in range(len(reads)):
-        name = reads.names[i]
-        if isinstance(name, str):
-            name = name.encode("latin-1")
-        seq = raw[off[i]:off[i + 1]]
-        if dist[i] < 0:
-            out.append(b"%s\t-1\tNA\t%s\n" % (name, seq[-1:-1]))
-        else:
-            ei = int(e[i])
-            out.append(b"%s\t%d\t%d\t%s\n" % (name, dist[i], loc[i], seq[int(s[i]):ei or None]))
-    return b"".join(out)
+    data, _ = _lib.io_format_lr_bc(reads.name_bytes, reads.name_offsets, reads.read_bytes, reads.offsets, dist, loc, s,
+                                   e, gzip_level=gzip_level, threads=threads)
+    return data
 
 
-def output_matches(reads: Reads, filtered, outfile):
+def output_matches(reads: Reads, filtered, outfile, threads=None):
     """gzip when -o is given (whatever its suffix, scTagger.py:377-378), STDOUT otherwise."""
     print(f"Writng to {outfile}", file=sys.stderr)
-    data = format_rows(reads, filtered)
     if outfile:
-        with gzip.open(outfile, "wb") as f:
-            f.write(data)
+        with open(outfile, "wb") as f:
+            f.write(format_rows(reads, filtered, gzip_level=GZIP_LEVEL, threads=threads))
     else:
-        sys.stdout.buffer.write(data)
+        sys.stdout.buffer.write(format_rows(reads, filtered, threads=threads))
         sys.stdout.buffer.flush()
 
 
 def extract_lr_bc(args):
     """Stage driver, same steps as reference scTagger.py:362-383 (plotting, -p, is not part of this path)."""
-    reads = read_fastqs(args.reads, args.gzipped)
+    reads = read_fastqs(args.reads, args.gzipped, args.threads)
     alns = get_lr_bc_alns(reads, args.threads, adapter=args.short_read_adapter,
                           devices=getattr(args, "devices", None))
     if len(args.ranges[0]) + len(args.ranges[1]) == 0:
@@ -270,5 +266,5 @@ def extract_lr_bc(args):
     else:
         range_dicts = RangeDicts(args.ranges, inclusive_end=True)
     filtered = get_filter_alns(alns, range_dicts, args.num_bp_after, args.threads)
-    output_matches(reads, filtered, args.outfile)
+    output_matches(reads, filtered, args.outfile, args.threads)
     return alns, filtered

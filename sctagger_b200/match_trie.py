@@ -14,6 +14,7 @@ The compute is done by `libsctagger_b200.so` (C-ABI in include/sctagger_b200.h) 
 from __future__ import annotations
 
 import gzip
+import os
 import sys
 from dataclasses import dataclass
 
@@ -65,32 +66,33 @@ def read_sr_barcodes(path: str):
 
 @dataclass
 class LongReads:
-    names: list            # lr_names
-    seg_bytes: np.ndarray  # uint8, all segments concatenated (lr_segs)
-    offsets: np.ndarray    # int64[n+1] (lr_segs_idxs)
+    name_bytes: np.ndarray    # uint8, all read names concatenated (lr_names)
+    name_offsets: np.ndarray  # int64[n+1]
+    seg_bytes: np.ndarray     # uint8, all segments concatenated (lr_segs)
+    offsets: np.ndarray       # int64[n+1] (lr_segs_idxs)
 
     def __len__(self):
-        return len(self.names)
+        return int(self.offsets.shape[0]) - 1
+
+    @property
+    def names(self):
+        """lr_names as a list of bytes (built on demand; the stage itself never needs it)."""
+        raw, o = self.name_bytes.tobytes(), self.name_offsets.tolist()
+        return [raw[o[i]:o[i + 1]] for i in range(len(self))]
 
     def segment(self, rid: int) -> bytes:
         return self.seg_bytes[self.offsets[rid]:self.offsets[rid + 1]].tobytes()
 
 
-def read_long_reads(path: str) -> LongReads:
-    """Column 0 = read name, column 3 = segment (reference scTagger.py:602-628).
-    Rows with fewer than four columns raise IndexError like the reference (scTagger.py:613-614)."""
+def read_long_reads(path: str, threads=None) -> LongReads:
+    """Column 0 = read name, column 3 = segment (reference scTagger.py:602-628); gzip iff the name ends with '.gz'.
+    Rows with fewer than four columns raise IndexError like the reference (scTagger.py:613-614).  Parsed natively
+    (sct_io_read_long_reads: threaded, two memchr passes) instead of the reference's per-character Python loop."""
+    from . import _lib
     print("Reading long reads barcodes")
-    names, segs = [], []
-    for l in _lines(_read_all(path)):
-        cols = l.rstrip(b"\r").split(b"\t")
-        names.append(cols[0])
-        segs.append(cols[3])
-    offsets = np.zeros(len(segs) + 1, dtype=np.int64)
-    if segs:
-        np.cumsum(np.fromiter((len(s) for s in segs), dtype=np.int64, count=len(segs)), out=offsets[1:])
-    seg_bytes = np.frombuffer(b"".join(segs), dtype=np.uint8)
-    print(f"There are {len(names):,} LRs")
-    return LongReads(names, seg_bytes, offsets)
+    reads = LongReads(*_lib.io_read_long_reads(path, threads))
+    print(f"There are {len(reads):,} LRs")
+    return reads
 
 
 @dataclass
@@ -131,36 +133,33 @@ def run_get_matches_prefix(barcodes, reads: LongReads, max_error: int, threads: 
                                mem_gb=mem_gb, devices=devices)
 
 
+def format_reads_rows(reads: LongReads, result: MatchResult, barcodes, gzip_level: int = 0, threads=None) -> bytes:
+    """TSV rows exactly as the reference writes them (scTagger.py:777-789): only reads with a match, in read order;
+    `name, e, n_ties, segment, comma-joined tied barcodes` (RC string for strand False).  gzip_level > 0 returns the
+    same rows as gzip members.  Formatted natively (sct_io_format_matches)."""
+    from . import _lib
+    bl = len(barcodes[0]) if len(barcodes) else 1
+    bm = barcode_matrix(barcodes, bl) if len(barcodes) else np.zeros((0, 1), dtype=np.uint8)
+    data, _ = _lib.io_format_matches(reads.name_bytes, reads.name_offsets, reads.seg_bytes, reads.offsets, result, bm,
+                                     gzip_level=gzip_level, threads=threads)
+    return data
+
+
 def format_rows(names, reads_seg_bytes: np.ndarray, offsets: np.ndarray, result: MatchResult, barcodes) -> bytes:
-    """TSV rows exactly as the reference writes them (scTagger.py:777-789): only reads with a match,
-    in read order; `name, e, n_ties, segment, comma-joined tied barcodes` (RC string for strand False)."""
-    bc = [b.encode("latin-1") for b in barcodes]
-    rc_cache = {}
-    raw = reads_seg_bytes.tobytes()
-    out = []
-    hit = np.nonzero(result.min_ed >= 0)[0]
-    tie_off = result.tie_offsets
-    ids = result.tie_ids
-    for rid in hit.tolist():
-        parts = []
-        for pid in ids[tie_off[rid]:tie_off[rid + 1]].tolist():
-            if pid & 1:
-                parts.append(bc[pid >> 1])
-            else:
-                r = rc_cache.get(pid >> 1)
-                if r is None:
-                    r = rc_cache[pid >> 1] = rev_compl(barcodes[pid >> 1]).encode("latin-1")
-                parts.append(r)
-        name = names[rid]
-        if isinstance(name, str):
-            name = name.encode("latin-1")
-        out.append(b"%s\t%d\t%d\t%s\t%s\n" % (name, result.min_ed[rid], result.n_ties[rid],
-                                             raw[offsets[rid]:offsets[rid + 1]], b",".join(parts)))
-    return b"".join(out)
+    """`format_reads_rows` for names given as a list (or a LongReads' `names`)."""
+    from . import _lib
+    nb, no = _lib.pack_names(names)
+    return format_reads_rows(LongReads(nb, no, reads_seg_bytes, offsets), result, barcodes)
+
+
+# `gzip.open` in the reference compresses at level 9 (30 s per 1 M rows on one core); level 4 costs 7 % more bytes and
+# 0.25 s on 8 threads.  Only the decompressed bytes are comparable between writers.  SCT_GZIP_LEVEL=1..9 overrides.
+GZIP_LEVEL = min(9, max(1, int(os.environ.get("SCT_GZIP_LEVEL", "4"))))
 
 
 def write_matches(outfile, data: bytes):
-    """gzip iff the name ends with 'gz', plain file otherwise, STDOUT when absent (scTagger.py:770-776)."""
+    """Plain bytes `data` -> gzip iff the name ends with 'gz', plain file otherwise, STDOUT when absent
+    (scTagger.py:770-776)."""
     if outfile:
         if outfile.endswith("gz"):
             with gzip.open(outfile, "wb") as f:
@@ -173,18 +172,30 @@ def write_matches(outfile, data: bytes):
         sys.stdout.buffer.flush()
 
 
-def match_trie_bytes(args) -> bytes:
-    """Everything of reference scTagger.py:758-790 except opening the output file: -> the TSV rows."""
+def _match_trie_result(args):
     barcodes = read_sr_barcodes(args.short_read_barcodes)
     barcode_lens = {len(b) for b in barcodes}
     assert barcode_lens == {args.barcode_length}, barcode_lens
-    reads = read_long_reads(args.long_read_segments)
+    reads = read_long_reads(args.long_read_segments, args.threads)
     result = run_get_matches_prefix(barcodes, reads, max_error=args.max_error, threads=args.threads,
                                     barcode_length=args.barcode_length, mem_gb=args.mem,
                                     devices=getattr(args, "devices", None))
-    return format_rows(reads.names, reads.seg_bytes, reads.offsets, result, barcodes)
+    return barcodes, reads, result
+
+
+def match_trie_bytes(args) -> bytes:
+    """Everything of reference scTagger.py:758-790 except opening the output file: -> the TSV rows."""
+    barcodes, reads, result = _match_trie_result(args)
+    return format_reads_rows(reads, result, barcodes)
 
 
 def match_trie(args):
-    """Stage driver, same steps as reference scTagger.py:758-790."""
-    write_matches(args.outfile, match_trie_bytes(args))
+    """Stage driver, same steps as reference scTagger.py:758-790.  With a `gz` output name the rows are compressed by
+    the native writer (parallel gzip members) and written as they are."""
+    barcodes, reads, result = _match_trie_result(args)
+    if args.outfile and args.outfile.endswith("gz"):
+        data = format_reads_rows(reads, result, barcodes, gzip_level=GZIP_LEVEL)
+        with open(args.outfile, "wb") as f:
+            f.write(data)
+    else:
+        write_matches(args.outfile, format_reads_rows(reads, result, barcodes))

@@ -138,17 +138,27 @@ def write_barcodes(path, barcodes: np.ndarray, seed: int):
         f.write(b"".join(row.tobytes() + b"\t%d\n" % c for row, c in zip(barcodes, counts)))
 
 
+def read_names(n: int, first_index: int = 0):
+    """`read{i}` for i = first_index .. first_index+n-1 as (name_bytes, name_offsets)."""
+    a = np.char.add(b"read", np.arange(first_index, first_index + n).astype("S20"))
+    u8 = a.view(np.uint8).reshape(n, -1) if n else np.zeros((0, 1), dtype=np.uint8)
+    mask = u8 != 0
+    off = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(mask.sum(axis=1), out=off[1:])
+    return np.ascontiguousarray(u8[mask]), off
+
+
 def write_segments(path, seg_bytes: np.ndarray, offsets: np.ndarray, first_index: int = 0):
-    sb = seg_bytes.tobytes()
-    with _open_w(path) as f:
-        buf = []
-        for i in range(offsets.shape[0] - 1):
-            s = sb[offsets[i]:offsets[i + 1]]
-            buf.append(b"read%d\t0\t0\t%s\n" % (first_index + i, s))
-            if len(buf) >= 65536:
-                f.write(b"".join(buf))
-                buf = []
-        f.write(b"".join(buf))
+    """`read{i} \\t 0 \\t 0 \\t segment` rows — the -lr format `output_matches` of extract_lr_bc writes
+    (scTagger.py:317-320) — through the native writer (gzip members when the name ends with .gz)."""
+    from . import _lib
+    n = offsets.shape[0] - 1
+    nb, no = read_names(n, first_index)
+    z = np.zeros(max(n, 1), dtype=np.int64)
+    data, _ = _lib.io_format_lr_bc(nb, no, seg_bytes, offsets, z, z, z, z,
+                                   gzip_level=1 if str(path).endswith(".gz") else 0)
+    with open(path, "wb") as f:
+        f.write(data)
 
 
 ADAPTER = b"CTACACGACGCTCTTCCGATCT"   # reference default -sa (scTagger.py:42)
