@@ -379,42 +379,85 @@ def concat_results(parts):
     return MatchResult(min_ed, n_ties, np.concatenate(offs), ids)
 
 
-def match_segments(barcodes: np.ndarray, seg_bytes: np.ndarray, offsets: np.ndarray, max_error: int,
-                   threads: int = 16, mem_gb: float = 16.0, devices=None, **options):
-    """All segments against all barcodes on one or several GPUs of this process.
-    devices: None = device 0; an int N = devices 0..N-1; or an explicit list.  Reads are split into
-    contiguous ranges, one host thread + one handle per GPU (ctypes releases the GIL), results are
-    concatenated in read order."""
-    if devices is None:
-        devices = [0]
-    elif isinstance(devices, int):
-        devices = list(range(devices))
-    devices = list(devices)
-    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
-    n = offsets.shape[0] - 1
-    if len(devices) == 1:
-        with Matcher(barcodes, max_error, threads, mem_gb, devices[0], **options) as m:
-            return m.match(seg_bytes, offsets)
-    bounds = shard_bounds(n, len(devices))
-    results = [None] * len(devices)
-    errors = []
+class MatcherGroup:
+    """One Matcher per GPU of this process (handles are created concurrently: CUDA context creation is the slow part and
+    the CLI overlaps it with reading the -lr file).  Reads are split into contiguous ranges, one host thread per GPU
+    (ctypes releases the GIL), results are concatenated in read order; no collective."""
 
-    def work(i):
-        try:
-            a, b = bounds[i]
-            with Matcher(barcodes, max_error, threads, mem_gb / len(devices), devices[i], **options) as m:
-                results[i] = m.match(seg_bytes, offsets[a:b + 1])
-        except Exception as e:  # re-raised in the caller
-            errors.append(e)
+    def __init__(self, barcodes: np.ndarray, max_error: int, threads: int = 16, mem_gb: float = 16.0, devices=None,
+                 **options):
+        if devices is None:
+            devices = [0]
+        elif isinstance(devices, int):
+            devices = list(range(devices))
+        self.devices = list(devices)
+        g = len(self.devices)
+        self.matchers = [None] * g
+        errors = []
 
-    ts = [threading.Thread(target=work, args=(i,)) for i in range(len(devices))]
+        def make(i):
+            try:
+                self.matchers[i] = Matcher(barcodes, max_error, threads, mem_gb / g, self.devices[i], **options)
+            except Exception as e:      # re-raised in the caller
+                errors.append(e)
+
+        _run_threads(make, g)
+        if errors:
+            self.close()
+            raise errors[0]
+
+    def match(self, seg_bytes: np.ndarray, offsets: np.ndarray):
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        n = offsets.shape[0] - 1
+        g = len(self.matchers)
+        if g == 1:
+            return self.matchers[0].match(seg_bytes, offsets)
+        bounds = shard_bounds(n, g)
+        results = [None] * g
+        errors = []
+
+        def work(i):
+            try:
+                a, b = bounds[i]
+                results[i] = self.matchers[i].match(seg_bytes, offsets[a:b + 1])
+            except Exception as e:
+                errors.append(e)
+
+        _run_threads(work, g)
+        if errors:
+            raise errors[0]
+        return concat_results(results)
+
+    def close(self):
+        for m in self.matchers:
+            if m is not None:
+                m.close()
+        self.matchers = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+def _run_threads(fn, n):
+    if n == 1:
+        fn(0)
+        return
+    ts = [threading.Thread(target=fn, args=(i,)) for i in range(n)]
     for t in ts:
         t.start()
     for t in ts:
         t.join()
-    if errors:
-        raise errors[0]
-    return concat_results(results)
+
+
+def match_segments(barcodes: np.ndarray, seg_bytes: np.ndarray, offsets: np.ndarray, max_error: int,
+                   threads: int = 16, mem_gb: float = 16.0, devices=None, **options):
+    """All segments against all barcodes on one or several GPUs of this process.
+    devices: None = device 0; an int N = devices 0..N-1; or an explicit list."""
+    with MatcherGroup(barcodes, max_error, threads, mem_gb, devices, **options) as g:
+        return g.match(seg_bytes, offsets)
 
 
 # ---- native host I/O (sct_io_*): parse / format / gzip with the host threads, no GPU involved ---------------------------

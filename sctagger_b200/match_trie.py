@@ -173,13 +173,35 @@ def write_matches(outfile, data: bytes):
 
 
 def _match_trie_result(args):
+    import threading
+    from . import _lib
     barcodes = read_sr_barcodes(args.short_read_barcodes)
     barcode_lens = {len(b) for b in barcodes}
     assert barcode_lens == {args.barcode_length}, barcode_lens
-    reads = read_long_reads(args.long_read_segments, args.threads)
-    result = run_get_matches_prefix(barcodes, reads, max_error=args.max_error, threads=args.threads,
-                                    barcode_length=args.barcode_length, mem_gb=args.mem,
-                                    devices=getattr(args, "devices", None))
+    # the GPU handles (CUDA context + barcode index) are created while the host parses the -lr file
+    box = {}
+
+    def make_group():
+        try:
+            box["group"] = _lib.MatcherGroup(barcode_matrix(barcodes, args.barcode_length), args.max_error, args.threads,
+                                             args.mem, getattr(args, "devices", None))
+        except Exception as e:
+            box["error"] = e
+
+    t = threading.Thread(target=make_group)
+    t.start()
+    try:
+        reads = read_long_reads(args.long_read_segments, args.threads)
+    except BaseException:
+        t.join()
+        if "group" in box:
+            box["group"].close()
+        raise
+    t.join()
+    if "error" in box:
+        raise box["error"]
+    with box["group"] as group:
+        result = group.match(reads.seg_bytes, reads.offsets)
     return barcodes, reads, result
 
 
