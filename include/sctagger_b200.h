@@ -167,10 +167,17 @@ int sct_align_set_option(sct_align_handle *h, const char *key, int64_t value);
  *   sct_io_format_lr_bc     <- output_matches of extract_lr_bc (scTagger.py:317-320): `rname \t dist \t loc \t
  *        seq[s:e or None]` for every read; dist < 0 = rejected by filter_aln: `-1`, `NA`, empty sequence.
  *   The buffers stay valid until the matching *_free call.
+ *   sct_io_read_lr_bc_segments <- the -i reader of extract_sr_bc_from_lr (scTagger.py:811-822): `_,_,p,seg = l.split('\t')`,
+ *        exactly four columns (else SCT_E_FORMAT, the reference's ValueError); rows with p == "NA" are skipped; only the
+ *        segments are kept (no names).
+ *   sct_io_read_whitelist   <- the -wl reader (scTagger.py:793-799): every line minus its last character (`l[:-1]`),
+ *        returned as the "segments" of the handle, line order = barcode index.
  */
 typedef struct sct_reads sct_reads;
 typedef struct sct_buffer sct_buffer;
 int sct_io_read_long_reads(const char *path, int32_t threads, sct_reads **out);
+int sct_io_read_lr_bc_segments(const char *path, int32_t threads, sct_reads **out);
+int sct_io_read_whitelist(const char *path, int32_t threads, sct_reads **out);
 int sct_io_read_fastqs(const char *path, int32_t gzipped, int32_t threads, sct_reads **out);
 int sct_io_reads_info(sct_reads *r, int64_t *n, const uint8_t **name_bytes, const int64_t **name_offsets,
                       const uint8_t **seg_bytes, const int64_t **seg_offsets);
@@ -185,6 +192,39 @@ int sct_io_format_lr_bc(const uint8_t *name_bytes, const int64_t *name_offsets, 
                         const int64_t *s, const int64_t *e, int32_t gzip_level, int32_t threads, sct_buffer **out);
 int sct_io_buffer_info(sct_buffer *b, const uint8_t **data, int64_t *size, int64_t *rows);
 int sct_io_buffer_free(sct_buffer *b);
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * extract_sr_bc_from_lr: exact whitelist search.  The reference's seam is the loop
+ *     A = ahocorasick.Automaton(); A.add_word(bc, idx) ...; A.add_word(rev_compl(bc), -idx) ...     scTagger.py:802-809
+ *     for every segment: hits = tuple(A.iter(seg)); if len(hits) == 1: C[abs(hits[0][1])] += 1     scTagger.py:819-827
+ * pyahocorasick is a third-party dependency that is not part of the reference tree (env.yaml, unpinned); the semantics
+ * implemented are its documented ones — add_word on an existing key replaces the value, iter reports every occurrence
+ * of every key in order of its end position — restated in oracle/wl_oracle.py (parity with pyahocorasick unpinned).
+ *
+ *   sct_wl_create   <- the automaton: words = the whitelist lines as the reference reads them (concatenated bytes +
+ *                      n_words+1 offsets, line order = barcode index).  Blank lines add no word; all other words must
+ *                      share one length <= 31 (SCT_E_UNSUPPORTED otherwise; the 10x whitelists are all 16-mers).  Bytes
+ *                      are compared literally (a word holding a byte outside ACGT only matches that byte).
+ *   sct_wl_count    <- the per-segment loop over one batch of segments (HOST buffers; streamed in chunks).  Counts are
+ *                      accumulated on the device across calls.  Optional per-segment outputs (may be NULL):
+ *                      n_hits[r] = len(hits), hit_word[r] = abs(value) of the first hit or -1.
+ *   sct_wl_result   <- the Counter C in insertion order: barcode indices and counts of every barcode counted so far,
+ *                      ordered by the first segment that counted it (library-owned until the next call / destroy).
+ *   sct_wl_reset    clears the counts.   sct_wl_stage / sct_wl_run_staged: device-resident timing of one batch.
+ *   sct_wl_stats    [0] kernel launches, [1] chunks of the last call, [2] host->device bytes, [3] device->host bytes,
+ *                   [4] distinct packed keys in the table, [5] segments so far, [6] table slots, [7] literal (non-ACGT) words.
+ */
+typedef struct sct_wl_handle sct_wl_handle;
+int sct_wl_create(int device, const uint8_t *word_bytes, const int64_t *word_offsets, int64_t n_words, int32_t threads,
+                  sct_wl_handle **out);
+int sct_wl_destroy(sct_wl_handle *h);
+int sct_wl_count(sct_wl_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n, int32_t *n_hits,
+                 int32_t *hit_word);
+int sct_wl_result(sct_wl_handle *h, int64_t *n_unique, const int32_t **word_idx, const int64_t **count);
+int sct_wl_reset(sct_wl_handle *h);
+int sct_wl_stage(sct_wl_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n);
+int sct_wl_run_staged(sct_wl_handle *h, float *kernel_ms);
+int sct_wl_stats(sct_wl_handle *h, int64_t stats[8]);
 
 #ifdef __cplusplus
 }

@@ -23,6 +23,9 @@ EXPORTS = (
     "sct_align_stats", "sct_align_set_option",
     "sct_io_read_long_reads", "sct_io_read_fastqs", "sct_io_reads_info", "sct_io_reads_free",
     "sct_io_format_matches", "sct_io_format_lr_bc", "sct_io_buffer_info", "sct_io_buffer_free",
+    "sct_io_read_lr_bc_segments", "sct_io_read_whitelist",
+    "sct_wl_create", "sct_wl_destroy", "sct_wl_count", "sct_wl_result", "sct_wl_reset", "sct_wl_stage",
+    "sct_wl_run_staged", "sct_wl_stats",
 )
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
@@ -97,6 +100,25 @@ def lib():
             L.sct_align_set_option.argtypes = [_vp, ctypes.c_char_p, ctypes.c_int64]
             L.sct_io_read_long_reads.restype = ctypes.c_int
             L.sct_io_read_long_reads.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.POINTER(_vp)]
+            for f in (L.sct_io_read_lr_bc_segments, L.sct_io_read_whitelist):
+                f.restype = ctypes.c_int
+                f.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.POINTER(_vp)]
+            L.sct_wl_create.restype = ctypes.c_int
+            L.sct_wl_create.argtypes = [ctypes.c_int, _u8p, _i64p, ctypes.c_int64, ctypes.c_int32, ctypes.POINTER(_vp)]
+            L.sct_wl_destroy.restype = ctypes.c_int
+            L.sct_wl_destroy.argtypes = [_vp]
+            L.sct_wl_count.restype = ctypes.c_int
+            L.sct_wl_count.argtypes = [_vp, _u8p, _i64p, ctypes.c_int64, _i32p, _i32p]
+            L.sct_wl_result.restype = ctypes.c_int
+            L.sct_wl_result.argtypes = [_vp, _i64p, ctypes.POINTER(_i32p), ctypes.POINTER(_i64p)]
+            L.sct_wl_reset.restype = ctypes.c_int
+            L.sct_wl_reset.argtypes = [_vp]
+            L.sct_wl_stage.restype = ctypes.c_int
+            L.sct_wl_stage.argtypes = [_vp, _u8p, _i64p, ctypes.c_int64]
+            L.sct_wl_run_staged.restype = ctypes.c_int
+            L.sct_wl_run_staged.argtypes = [_vp, _f32p]
+            L.sct_wl_stats.restype = ctypes.c_int
+            L.sct_wl_stats.argtypes = [_vp, _i64p]
             L.sct_io_read_fastqs.restype = ctypes.c_int
             L.sct_io_read_fastqs.argtypes = [ctypes.c_char_p, ctypes.c_int32, ctypes.c_int32, ctypes.POINTER(_vp)]
             L.sct_io_reads_info.restype = ctypes.c_int
@@ -499,6 +521,26 @@ def io_read_fastqs(path: str, gzipped: bool = False, threads=None):
     return _take_reads(h)
 
 
+def io_read_lr_bc_segments(path: str, threads=None):
+    """sct_io_read_lr_bc_segments -> (seg_bytes, seg_offsets) of the rows whose location column is not 'NA'; a row that
+    does not have exactly four columns raises ValueError like the reference's tuple unpacking (scTagger.py:820)."""
+    h = _vp()
+    try:
+        _check(lib().sct_io_read_lr_bc_segments(os.fsencode(path), host_threads(threads), ctypes.byref(h)))
+    except IndexError as e:
+        raise ValueError(str(e)) from None
+    _, _, sb, so = _take_reads(h)
+    return sb, so
+
+
+def io_read_whitelist(path: str, threads=None):
+    """sct_io_read_whitelist -> (word_bytes, word_offsets): every line minus its last character (scTagger.py:798)."""
+    h = _vp()
+    _check(lib().sct_io_read_whitelist(os.fsencode(path), host_threads(threads), ctypes.byref(h)))
+    _, _, wb, wo = _take_reads(h)
+    return wb, wo
+
+
 def _take_buffer(h):
     try:
         data = _u8p()
@@ -555,3 +597,74 @@ def pack_names(names):
     if enc:
         np.cumsum(np.fromiter((len(x) for x in enc), dtype=np.int64, count=len(enc)), out=off[1:])
     return np.frombuffer(b"".join(enc), dtype=np.uint8), off
+
+
+WL_STAT_NAMES = ("launches", "chunks", "h2d_bytes", "d2h_bytes", "table_keys", "segments", "table_slots", "literal_words")
+
+
+class Whitelist:
+    """One handle = one GPU holding the whitelist hash table (sct_wl_create .. sct_wl_destroy): the Aho-Corasick
+    automaton and Counter loop of extract_sr_bc_from_lr (reference scTagger.py:802-827)."""
+
+    def __init__(self, word_bytes: np.ndarray, word_offsets: np.ndarray, threads: int = 16, device: int = 0):
+        wb = _as_u8(word_bytes)
+        wo = _i64(word_offsets)
+        self.n_words = int(np.asarray(word_offsets).shape[0]) - 1
+        self._h = _vp()
+        _check(lib().sct_wl_create(int(device), _ptr(wb, ctypes.c_uint8), _ptr(wo, ctypes.c_int64), self.n_words,
+                                   int(threads), ctypes.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().sct_wl_destroy(self._h)
+            self._h = _vp()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def count(self, seg_bytes: np.ndarray, offsets: np.ndarray, per_segment: bool = False):
+        """Adds one batch of segments to the counts; per_segment=True -> (n_hits int32[n], hit_word int32[n])."""
+        sb = _as_u8(seg_bytes)
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        n = off.shape[0] - 1
+        if per_segment:
+            nh = np.empty(max(n, 1), dtype=np.int32)
+            hw = np.empty(max(n, 1), dtype=np.int32)
+            _check(lib().sct_wl_count(self._h, _ptr(sb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), n,
+                                      _ptr(nh, ctypes.c_int32), _ptr(hw, ctypes.c_int32)))
+            return nh[:n], hw[:n]
+        _check(lib().sct_wl_count(self._h, _ptr(sb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), n, None, None))
+        return None
+
+    def result(self):
+        """The Counter in insertion order -> (barcode index int32[u], count int64[u])."""
+        n = ctypes.c_int64(0)
+        idx, cnt = _i32p(), _i64p()
+        _check(lib().sct_wl_result(self._h, ctypes.byref(n), ctypes.byref(idx), ctypes.byref(cnt)))
+        u = int(n.value)
+        if u == 0:
+            return np.zeros(0, dtype=np.int32), np.zeros(0, dtype=np.int64)
+        return np.ctypeslib.as_array(idx, shape=(u,)).copy(), np.ctypeslib.as_array(cnt, shape=(u,)).copy()
+
+    def reset(self):
+        _check(lib().sct_wl_reset(self._h))
+
+    def stage(self, seg_bytes: np.ndarray, offsets: np.ndarray):
+        sb = _as_u8(seg_bytes)
+        off = np.ascontiguousarray(offsets, dtype=np.int64)
+        _check(lib().sct_wl_stage(self._h, _ptr(sb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), off.shape[0] - 1))
+
+    def run_staged(self) -> float:
+        ms = ctypes.c_float(0)
+        _check(lib().sct_wl_run_staged(self._h, ctypes.byref(ms)))
+        return float(ms.value)
+
+    def stats(self) -> dict:
+        s = np.zeros(8, dtype=np.int64)
+        _check(lib().sct_wl_stats(self._h, _ptr(s, ctypes.c_int64)))
+        return dict(zip(WL_STAT_NAMES, s.tolist()))

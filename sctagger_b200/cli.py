@@ -54,6 +54,19 @@ def build_parser() -> argparse.ArgumentParser:
                    help="Number of bases after the end of the SR adapter alignment to generate. Default: 20")
     q.add_argument("--gpus", type=int, default=None, help="Number of GPUs to shard the reads over. Default: 1")
     q.add_argument("--devices", type=str, default=None, help="Comma separated CUDA device indices (overrides --gpus)")
+    w = subparsers.add_parser("extract_sr_bc_from_lr")      # scTagger.py:67-79
+    w.add_argument("-i", "--input", type=str, required=True, help="Input TSV file generated from extract_lr_bc step")
+    w.add_argument("-o", "--outfile", type=str, default=None, help="Path to output file. Default: STDOUT")
+    w.add_argument("-wl", "--barcode-whitelist", type=str, required=True,
+                   help="Path to TXT barcode whiltelist such as 10x Chromimum v3 3M-february-2018.txt.gz barcode file")
+    w.add_argument("--thresh", type=float, default=0.005,
+                   help="Percentage theshold required per step to continue adding read barcodes. Default: 0.005")
+    w.add_argument("--step-size", type=int, default=1000,
+                   help="Number of barcodes processed at a time and whose sum is used to check against the theshold. "
+                        "Default: 1000")
+    w.add_argument("--max-barcode-cnt", type=int, default=25_000, help="Max number of barcodes to keep. Default: 25000")
+    w.add_argument("--gpus", type=int, default=None, help="(one GPU is used; the table is not sharded)")
+    w.add_argument("--devices", type=str, default=None, help="CUDA device index")
     return parser
 
 
@@ -73,6 +86,11 @@ def parse_args(argv=None):
         args.ranges = parse_ranges_flag(args.ranges)
         assert args.threads > 0
         _devices(args)
+    if args.subcommand == "extract_sr_bc_from_lr":   # scTagger.py:135-138
+        assert 0 <= args.thresh <= 1
+        assert 0 < args.step_size
+        assert 0 < args.max_barcode_cnt
+        _devices(args)
     if args.subcommand == "match_trie":      # scTagger.py:140-143
         assert args.mem > 0
         assert args.barcode_length > 0
@@ -89,6 +107,19 @@ def main(argv=None):
         from . import extract_lr_bc as lr
         print(args, file=sys.stderr)
         lr.extract_lr_bc(args)
+        return 0
+    if args.subcommand == "extract_sr_bc_from_lr":
+        from . import extract_sr_bc_from_lr as wl
+        with contextlib.redirect_stdout(sys.stderr):
+            print(args)
+            data = wl.extract_sr_bc_from_lr_bytes(args)
+        if args.outfile:
+            import gzip
+            with gzip.open(args.outfile, "wb", compresslevel=mt.GZIP_LEVEL) as f:
+                f.write(data)
+        else:
+            sys.stdout.buffer.write(data)
+            sys.stdout.buffer.flush()
         return 0
     # the reference prints the Namespace and its progress lines to STDOUT (scTagger.py:849, 604, 628, ...);
     # here they go to STDERR so that STDOUT output stays a clean TSV

@@ -108,16 +108,18 @@ inline int64_t count_lines(const uint8_t *p, const uint8_t *e) {
 }
 
 struct PieceCount {
-    int64_t lines = 0, name_bytes = 0, seg_bytes = 0, bad_line = -1;
+    int64_t lines = 0, seen = 0, name_bytes = 0, seg_bytes = 0, bad_line = -1;
 };
 
 }  // namespace
 
-extern "C" {
-
-// ---------------------------------------------------------------------------------------------------------------------
-int sct_io_read_long_reads(const char *path, int32_t threads, sct_reads **out) {
-    if (!path || !out) return fail(SCT_E_ARG, "sct_io_read_long_reads: null argument");
+// mode 0: read_long_reads (scTagger.py:602-628): >= 4 columns, column 0 = name, column 3 = segment.
+// mode 1: the -i reader of extract_sr_bc_from_lr (scTagger.py:811-820): `_,_,p,seg = l.split('\t')` — exactly 4 columns
+//         (anything else is the reference's ValueError), rows whose column 2 is `NA` are skipped, names are not kept.
+// mode 2: the whitelist reader of extract_sr_bc_from_lr (scTagger.py:798): every line minus its last character
+//         (`l[:-1]`: the newline — or, on a last line without one, a real character, as in the reference).
+static int read_tsv(const char *path, int32_t threads, int mode, sct_reads **out) {
+    if (!path || !out) return fail(SCT_E_ARG, "sct_io_read: null argument");
     *out = nullptr;
     sct_reads *r = new (std::nothrow) sct_reads;
     if (!r) return fail(SCT_E_NOMEM, "out of memory");
@@ -142,34 +144,48 @@ int sct_io_read_long_reads(const char *path, int32_t threads, sct_reads **out) {
             while (p < e) {
                 const uint8_t *nl = (const uint8_t *)memchr(p, '\n', (size_t)(e - p));
                 const uint8_t *le = nl ? nl : e;
+                if (mode == 2 && !nl) --le;                                // l[:-1] on a last line without '\n'
                 while (le > p && le[-1] == '\r') --le;                     // text mode: "\r\n" reads as "\n"
+                if (mode == 2) {
+                    c.seg_bytes += le - p;
+                    ++c.lines, ++c.seen;
+                    if (!nl) break;
+                    p = nl + 1;
+                    continue;
+                }
                 const uint8_t *c0 = (const uint8_t *)memchr(p, '\t', (size_t)(le - p));
                 const uint8_t *c1 = c0 ? (const uint8_t *)memchr(c0 + 1, '\t', (size_t)(le - c0 - 1)) : nullptr;
                 const uint8_t *c2 = c1 ? (const uint8_t *)memchr(c1 + 1, '\t', (size_t)(le - c1 - 1)) : nullptr;
-                if (!c2) {
-                    if (c.bad_line < 0) c.bad_line = c.lines;
+                const uint8_t *c3 = c2 ? (const uint8_t *)memchr(c2 + 1, '\t', (size_t)(le - c2 - 1)) : nullptr;
+                ++c.seen;
+                if (!c2 || (mode == 1 && c3)) {
+                    if (c.bad_line < 0) c.bad_line = c.seen - 1;
+                } else if (mode == 1 && c2 - c1 == 3 && c1[1] == 'N' && c1[2] == 'A') {
+                    // p == 'NA': skipped (scTagger.py:821-822)
                 } else {
-                    const uint8_t *c3 = (const uint8_t *)memchr(c2 + 1, '\t', (size_t)(le - c2 - 1));
-                    c.name_bytes += c0 - p;
+                    if (mode == 0) c.name_bytes += c0 - p;
                     c.seg_bytes += (c3 ? c3 : le) - (c2 + 1);
+                    ++c.lines;
                 }
-                ++c.lines;
                 if (!nl) break;
                 p = nl + 1;
             }
             pc[t] = c;
         });
-        int64_t n = 0, nb = 0, sb = 0;
+        int64_t n = 0, nb = 0, sb = 0, seen = 0;
         std::vector<int64_t> row0(nt + 1), nb0(nt + 1), sb0(nt + 1);
         for (int t = 0; t < nt; ++t) {
             if (pc[t].bad_line >= 0) {
-                const long long line = (long long)(n + pc[t].bad_line + 1);
+                const long long line = (long long)(seen + pc[t].bad_line + 1);
                 delete r;
+                if (mode == 1)
+                    return fail(SCT_E_FORMAT, "line %lld of %s does not have exactly 4 tab-separated columns (the "
+                                "reference's ValueError on `_,_,p,seg = ...`)", line, path);
                 return fail(SCT_E_FORMAT, "list index out of range (line %lld of %s has fewer than 4 tab-separated columns)",
                             line, path);
             }
             row0[t] = n, nb0[t] = nb, sb0[t] = sb;
-            n += pc[t].lines, nb += pc[t].name_bytes, sb += pc[t].seg_bytes;
+            n += pc[t].lines, nb += pc[t].name_bytes, sb += pc[t].seg_bytes, seen += pc[t].seen;
         }
         row0[nt] = n, nb0[nt] = nb, sb0[nt] = sb;
         r->n = n;
@@ -184,19 +200,34 @@ int sct_io_read_long_reads(const char *path, int32_t threads, sct_reads **out) {
             while (p < e) {
                 const uint8_t *nl = (const uint8_t *)memchr(p, '\n', (size_t)(e - p));
                 const uint8_t *le = nl ? nl : e;
+                if (mode == 2 && !nl) --le;
                 while (le > p && le[-1] == '\r') --le;
+                if (mode == 2) {
+                    r->name_off[row] = 0;
+                    r->seg_off[row] = so;
+                    memcpy(r->seg_bytes.data() + so, p, (size_t)(le - p));
+                    so += le - p;
+                    ++row;
+                    if (!nl) break;
+                    p = nl + 1;
+                    continue;
+                }
                 const uint8_t *c0 = (const uint8_t *)memchr(p, '\t', (size_t)(le - p));
                 const uint8_t *c1 = (const uint8_t *)memchr(c0 + 1, '\t', (size_t)(le - c0 - 1));
                 const uint8_t *c2 = (const uint8_t *)memchr(c1 + 1, '\t', (size_t)(le - c1 - 1));
                 const uint8_t *c3 = (const uint8_t *)memchr(c2 + 1, '\t', (size_t)(le - c2 - 1));
                 const uint8_t *se = c3 ? c3 : le;
-                r->name_off[row] = no;
-                r->seg_off[row] = so;
-                memcpy(r->name_bytes.data() + no, p, (size_t)(c0 - p));
-                memcpy(r->seg_bytes.data() + so, c2 + 1, (size_t)(se - (c2 + 1)));
-                no += c0 - p;
-                so += se - (c2 + 1);
-                ++row;
+                if (!(mode == 1 && c2 - c1 == 3 && c1[1] == 'N' && c1[2] == 'A')) {
+                    r->name_off[row] = no;
+                    r->seg_off[row] = so;
+                    if (mode == 0) {
+                        memcpy(r->name_bytes.data() + no, p, (size_t)(c0 - p));
+                        no += c0 - p;
+                    }
+                    memcpy(r->seg_bytes.data() + so, c2 + 1, (size_t)(se - (c2 + 1)));
+                    so += se - (c2 + 1);
+                    ++row;
+                }
                 if (!nl) break;
                 p = nl + 1;
             }
@@ -211,6 +242,14 @@ int sct_io_read_long_reads(const char *path, int32_t threads, sct_reads **out) {
     *out = r;
     return SCT_OK;
 }
+
+extern "C" {
+
+int sct_io_read_long_reads(const char *path, int32_t threads, sct_reads **out) { return read_tsv(path, threads, 0, out); }
+
+int sct_io_read_lr_bc_segments(const char *path, int32_t threads, sct_reads **out) { return read_tsv(path, threads, 1, out); }
+
+int sct_io_read_whitelist(const char *path, int32_t threads, sct_reads **out) { return read_tsv(path, threads, 2, out); }
 
 // ---------------------------------------------------------------------------------------------------------------------
 static inline bool py_space(uint8_t c) { return c == ' ' || (c >= 9 && c <= 13); }   // str.split() / str.rstrip() set
