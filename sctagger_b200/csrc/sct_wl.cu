@@ -29,7 +29,7 @@ struct WSlot {
 struct sct_wl_handle {
     int device = 0, sm_count = 148, host_threads = 1;
     WlTable tab{};
-    int64_t n_words = 0, n_slots = 0, n_keys = 0;
+    int64_t n_words = 0, n_slots = 0, n_keys = 0, n_filter_bits = 0;
     uint8_t *d_odd = nullptr;
     int *d_odd_idx = nullptr, *d_odd_off = nullptr;
     unsigned int *d_counts = nullptr;
@@ -127,6 +127,7 @@ int sct_wl_destroy(sct_wl_handle *h) {
         free_wslot(s);
     }
     dev_free(h->tab.slots);
+    dev_free(h->tab.filter);
     dev_free(h->d_odd);
     dev_free(h->d_odd_idx);
     dev_free(h->d_odd_off);
@@ -231,12 +232,20 @@ int sct_wl_create(int device, const uint8_t *word_bytes, const int64_t *word_off
     while (slots < 4 * n_words) slots <<= 1;
     h->n_slots = slots;
     h->tab.mask = (unsigned long long)slots - 1;
+    int64_t fbits = 1 << 16;                              // up to 32 bits per key, at most 32 MiB (a quarter of L2)
+    int cap_log2 = 28;                                    // 32 MiB: measured best on B200 (2^26..2^29: 0.51, 0.43, 0.40, 0.44 ms)
+    if (const char *e = getenv("SCT_WL_FILTER_LOG2")) cap_log2 = std::max(16, std::min(33, atoi(e)));
+    while (fbits < 64 * n_words && fbits < ((int64_t)1 << cap_log2)) fbits <<= 1;
+    h->n_filter_bits = fbits;
+    h->tab.fmask = (unsigned long long)fbits - 1;
     h->tab.L = L;
     h->tab.n_odd = (int)odd.size();
     uint8_t *d_words = nullptr;
     unsigned int *d_n = nullptr;
     auto build = [&]() -> int {
         CUDA_TRY(cudaMalloc(&h->tab.slots, (size_t)slots * sizeof(ulonglong2)));
+        CUDA_TRY(cudaMalloc(&h->tab.filter, (size_t)(fbits / 8)));
+        CUDA_TRY(cudaMemset(h->tab.filter, 0, (size_t)(fbits / 8)));
         CUDA_TRY(cudaMalloc(&h->d_counts, (size_t)std::max<int64_t>(1, n_words) * sizeof(unsigned int)));
         CUDA_TRY(cudaMalloc(&h->d_first, (size_t)std::max<int64_t>(1, n_words) * sizeof(unsigned long long)));
         CUDA_TRY(cudaMalloc(&d_words, dense.size()));

@@ -8,9 +8,11 @@
 // with a rolling key.  The table is built on the GPU too: one thread per add_word call; the automaton's "a later add_word
 // of the same key replaces the value" is an atomicMax on (call order << 32 | barcode index).
 //
-// HBM-bound integer work: per window one 16-byte slot read = one 32-byte DRAM sector; the table
-// (2 x 2W keys at load factor <= 0.5, 16 B/slot: 512 MiB for the 6.8 M-barcode 10x whitelist) does not fit L2, the
-// segments stream through once.  No tensor cores, no collective.
+// HBM-bound integer work: per window one 16-byte slot read = one 32-byte DRAM sector is the
+// algorithmic traffic; the table (2 x 2W keys at load factor <= 0.5, 16 B/slot: 512 MiB for the 6.8 M-barcode 10x
+// whitelist) does not fit L2 and a random probe really costs a 128-byte line (ncu: 130 B of DRAM reads per probe), so a
+// one-hash bitmap of <= 32 MiB — a quarter of B200's 126 MB L2 — screens the windows first.  The segments stream through once.
+// No tensor cores, no collective.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -24,6 +26,8 @@ struct WlTable {
     ulonglong2 *slots;            // .x = key (WL_EMPTY = free), .y = call order << 32 | barcode index
     unsigned long long mask;      // n_slots - 1
     int L;                        // word length (1..31)
+    unsigned int *filter;         // one-hash membership bitmap sized to stay L2-resident (<= 32 MiB): bit set for every key
+    unsigned long long fmask;     // n_filter_bits - 1
     const uint8_t *odd;           // literal words: a byte outside ACGT, or a length other than L; concatenated
     const int *odd_off;           // n_odd + 1 offsets into odd
     const int *odd_idx;           // their barcode index
@@ -64,6 +68,8 @@ __global__ void __launch_bounds__(WL_THREADS) wl_insert_kernel(WlTable t, const 
         unsigned long long *kp = &t.slots[slot].x;
         const unsigned long long prev = atomicCAS(kp, WL_EMPTY, key);
         if (prev == WL_EMPTY || prev == key) {
+            const unsigned long long fb = (wl_hash(key) >> 24) & t.fmask;
+            atomicOr(&t.filter[fb >> 5], 1u << (fb & 31));
             atomicMax(&t.slots[slot].y, val);
             if (prev == WL_EMPTY) atomicAdd(n_inserted, 1u);
             return;
@@ -72,10 +78,16 @@ __global__ void __launch_bounds__(WL_THREADS) wl_insert_kernel(WlTable t, const 
     }
 }
 
+// A window that is not a whitelist word (~95 % of them) is answered by the filter word in L2; only filter positives
+// (true hits + n_keys / n_filter_bits false positives) touch the table in HBM, with streaming loads so that the table's
+// lines do not push the filter out of L2.
 __device__ __forceinline__ int wl_probe(const WlTable &t, unsigned long long key) {
-    unsigned long long slot = wl_hash(key) & t.mask;
+    const unsigned long long hsh = wl_hash(key);
+    const unsigned long long fb = (hsh >> 24) & t.fmask;
+    if (!((__ldg(&t.filter[fb >> 5]) >> (fb & 31)) & 1u)) return -1;
+    unsigned long long slot = hsh & t.mask;
     for (;;) {
-        const ulonglong2 e = __ldg(&t.slots[slot]);
+        const ulonglong2 e = __ldcs(&t.slots[slot]);
         if (e.x == key) return (int)(unsigned int)(e.y & 0xFFFFFFFFull);
         if (e.x == WL_EMPTY) return -1;
         slot = (slot + 1) & t.mask;
