@@ -179,6 +179,44 @@ def test_full_size_properties():
         assert ((int(pick[i]) << 1) | 1) in r.ties(i).tolist()
 
 
+@pytest.mark.parametrize("mr", [2, 3])
+def test_baseline_config_1m_seeded_equals_all_pairs_kernel(mr):
+    """BASELINE configs[1] (and configs[3]'s shape per GPU) at FULL size, 1 M segments x 25 k barcodes: the seeded kernel
+    (pigeonhole candidates + anchored pre-check) must give exactly what the all-pairs tile kernel gives (path=3 scores
+    every one of the 50 000 patterns per segment, no seeds, no pre-check), and what it gives with the pre-check off."""
+    bc = synth.make_barcodes(25_000, 1002)
+    sb, off = synth.make_segments(bc, 1_000_000, 2002)
+    with _lib.Matcher(bc, mr, 16) as m:
+        seeded = m.match(sb, off)
+        assert m.stats()["seed_candidates"] > 0
+    with _lib.Matcher(bc, mr, 16, path=3) as m:
+        tiles = m.match(sb, off)
+        assert m.stats()["seed_candidates"] == 0
+    _assert_same(seeded, tiles)
+    with _lib.Matcher(bc, mr, 16, seed_prefilter=0) as m:
+        _assert_same(m.match(sb, off), seeded)
+    rows = int((seeded.min_ed >= 0).sum())
+    assert rows == (887_994 if mr == 2 else 999_977)          # the bench's row counts for this seed
+
+
+def test_baseline_config_10m_chunked_streaming_is_shard_invariant():
+    """BASELINE configs[2] at FULL size: 10 M segments x 25 k barcodes, -mr 2, streamed in -m sized chunks.  The result of
+    the one 10 M call equals the concatenation of ten independent 1 M calls (what the 1/2/4/8-GPU sharding relies on), and
+    its first million equals the all-pairs-checked result of the test above (same generator seed per shard)."""
+    bc = synth.make_barcodes(25_000, 1002)
+    parts_in = [synth.make_segments(bc, 1_000_000, 2002 + i) for i in range(10)]
+    sb = np.concatenate([p[0] for p in parts_in])
+    off = np.concatenate([[0]] + [p[1][1:] + sum(int(q[1][-1]) for q in parts_in[:i]) for i, p in enumerate(parts_in)])
+    off = off.astype(np.int64)
+    with _lib.Matcher(bc, 2, 16, mem_gb=0.25) as m:          # small -m: many chunks per call
+        whole = m.match(sb, off)
+        assert m.stats()["chunks"] >= 10
+    with _lib.Matcher(bc, 2, 16) as m:
+        parts = [m.match(p[0], p[1]) for p in parts_in]
+    _assert_same(_lib.concat_results(parts), whole)
+    assert int((parts[0].min_ed >= 0).sum()) == 887_994
+
+
 def test_error_codes():
     bc = synth.make_barcodes(10, 1)
     with pytest.raises(_lib.SctError) as e:
