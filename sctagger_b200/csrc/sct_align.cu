@@ -344,6 +344,9 @@ int sct_align(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *rea
         TRY(finish(si));
         ASlot &s = h->slot[si];
         TRY(stage_chunk(h, s, read_bytes, read_offsets, first, cn));
+        // kernels of this chunk behind pass 1 of the chunk in flight (two streams would otherwise run both side by side,
+        // finish together and leave the GPU idle during the host's un-staging); the H2D above still overlaps
+        if (h->slot[1 - si].busy) CUDA_TRY(cudaStreamWaitEvent(s.stream, h->slot[1 - si].ev1, 0));
         TRY(enqueue_pass1(h, s));
         TRY(enqueue_fixed_copies(s));
         s.busy = true;

@@ -310,7 +310,12 @@ int complete_pass(sct_handle *h, Slot &s) {
 }
 
 // Copy chunk [first, first+n) of the caller's arrays into the slot's pinned staging and start H2D + pass.
-int start_chunk(sct_handle *h, Slot &s, const uint8_t *seg_bytes, const int64_t *off, int64_t first, int64_t n) {
+// `prev` = the slot holding the chunk before this one (still in flight): this chunk's kernels are ordered behind that
+// chunk's kernels with an event.  Without it the two streams run both chunks' persistent kernels side by side, they
+// finish together, and the GPU then idles while the host un-stages one chunk and stages the next — measured: the host
+// time (47 ms per 10 M segments) added to the kernel time instead of hiding behind it.  The H2D copy of this chunk
+// (issued before the wait) and the D2H copies of the previous one still overlap the kernels.
+int start_chunk(sct_handle *h, Slot &s, Slot *prev, const uint8_t *seg_bytes, const int64_t *off, int64_t first, int64_t n) {
     const int64_t b0 = off[first], nbytes = off[first + n] - b0;
     if (nbytes < 0) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
     TRY(ensure_slot(h, s, n, nbytes));
@@ -338,6 +343,7 @@ int start_chunk(sct_handle *h, Slot &s, const uint8_t *seg_bytes, const int64_t 
     CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
     h->stats[3] += nbytes + (n + 1) * (int64_t)sizeof(long long);
     h->stats[5] += 1;
+    if (prev && prev->busy) CUDA_TRY(cudaStreamWaitEvent(s.stream, prev->ev_end, 0));
     TRY(enqueue_pass(h, s, n));
     TRY(enqueue_result_copies(s));
     s.copies_enqueued = true;
@@ -661,7 +667,7 @@ int sct_match(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offset
         }
         const int si = (int)(chunk & 1);
         TRY(finish(si));
-        TRY(start_chunk(h, h->slot[si], seg_bytes, seg_offsets, first, cn));
+        TRY(start_chunk(h, h->slot[si], &h->slot[1 - si], seg_bytes, seg_offsets, first, cn));
         pending[si] = chunk;
         first += cn;
         ++chunk;
