@@ -113,6 +113,8 @@ struct PieceCount {
 
 }  // namespace
 
+int read_input_file(const char *path, bool gz, int threads, std::vector<uint8_t> &out);   // defined below
+
 // mode 0: read_long_reads (scTagger.py:602-628): >= 4 columns, column 0 = name, column 3 = segment.
 // mode 1: the -i reader of extract_sr_bc_from_lr (scTagger.py:811-820): `_,_,p,seg = l.split('\t')` — exactly 4 columns
 //         (anything else is the reference's ValueError), rows whose column 2 is `NA` are skipped, names are not kept.
@@ -126,7 +128,7 @@ static int read_tsv(const char *path, int32_t threads, int mode, sct_reads **out
     try {
         const size_t pl = strlen(path);
         const bool gz = pl >= 3 && strcmp(path + pl - 3, ".gz") == 0;      // scTagger.py:605
-        int rc = read_whole_file(path, gz, r->raw);
+        int rc = read_input_file(path, gz, threads, r->raw);
         if (rc != SCT_OK) {
             delete r;
             return rc;
@@ -262,7 +264,7 @@ int sct_io_read_fastqs(const char *path, int32_t gzipped, int32_t threads, sct_r
     try {
         const size_t pl = strlen(path);
         const bool gz = gzipped || (pl >= 3 && strcmp(path + pl - 3, ".gz") == 0);      // scTagger.py:164
-        int rc = read_whole_file(path, gz, r->raw);
+        int rc = read_input_file(path, gz, threads, r->raw);
         if (rc != SCT_OK) {
             delete r;
             return rc;
@@ -400,10 +402,26 @@ inline uint8_t *put_int(uint8_t *p, int64_t v) {
     return p;
 }
 
+// Every member written here carries its own sizes in the gzip header's FEXTRA field (RFC 1952 §2.3.1.1, subfield "SC":
+// u32 compressed member size, u32 uncompressed size — the BGZF idea with 32-bit sizes), which any gzip reader skips and
+// which lets read_whole_file() below inflate the members of such a file in parallel.
+constexpr int GZX_DATA_AT = 16;          // 10 fixed header bytes + XLEN(2) + SI1 SI2 LEN(2)
+constexpr int GZX_HEADER = GZX_DATA_AT + 8;
+
 int gzip_member(const std::vector<uint8_t> &in, int level, std::vector<uint8_t> &out) {
     z_stream z;
     memset(&z, 0, sizeof z);
     if (deflateInit2(&z, level, Z_DEFLATED, 15 + 16, 8, Z_DEFAULT_STRATEGY) != Z_OK) return -1;
+    gz_header gh;
+    memset(&gh, 0, sizeof gh);
+    uint8_t extra[12] = {'S', 'C', 8, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    gh.extra = extra;
+    gh.extra_len = sizeof extra;
+    gh.os = 255;
+    if (deflateSetHeader(&z, &gh) != Z_OK) {
+        deflateEnd(&z);
+        return -1;
+    }
     out.resize(deflateBound(&z, (uLong)in.size()) + 64);
     z.next_in = (Bytef *)in.data();
     z.avail_in = (uInt)in.size();
@@ -412,10 +430,86 @@ int gzip_member(const std::vector<uint8_t> &in, int level, std::vector<uint8_t> 
     const int rc = deflate(&z, Z_FINISH);
     const size_t produced = out.size() - z.avail_out;
     deflateEnd(&z);
-    if (rc != Z_STREAM_END) return -1;
+    if (rc != Z_STREAM_END || produced < (size_t)GZX_HEADER + 8 || produced > 0xFFFFFFFFull) return -1;
     out.resize(produced);
+    const uint32_t cs = (uint32_t)produced, us = (uint32_t)in.size();
+    for (int i = 0; i < 4; ++i) {
+        out[GZX_DATA_AT + i] = (uint8_t)(cs >> (8 * i));
+        out[GZX_DATA_AT + 4 + i] = (uint8_t)(us >> (8 * i));
+    }
     return 0;
 }
+
+}  // namespace
+
+// A .gz file whose members all carry the "SC" size subfield (written by gzip_member above) is inflated member by member
+// on the host threads; anything else (the reference's single-member files, foreign gzip) takes the serial zlib path.
+int read_gz_parallel(const char *path, int threads, std::vector<uint8_t> &out, bool *handled) {
+    *handled = false;
+    std::vector<uint8_t> raw;
+    int rc = read_whole_file(path, false, raw);
+    if (rc != SCT_OK) return rc;
+    struct Member { size_t at, csize, uoff, usize; };
+    std::vector<Member> ms;
+    size_t pos = 0, utotal = 0;
+    while (pos < raw.size()) {
+        const uint8_t *p = raw.data() + pos;
+        if (raw.size() - pos < (size_t)GZX_HEADER + 8 || p[0] != 0x1f || p[1] != 0x8b || p[2] != 8 || !(p[3] & 4) ||
+            p[10] != 12 || p[11] != 0 || p[12] != 'S' || p[13] != 'C' || p[14] != 8 || p[15] != 0)
+            return SCT_OK;                                   // not (only) our members: serial path
+        uint32_t cs = 0, us = 0;
+        for (int i = 0; i < 4; ++i) {
+            cs |= (uint32_t)p[GZX_DATA_AT + i] << (8 * i);
+            us |= (uint32_t)p[GZX_DATA_AT + 4 + i] << (8 * i);
+        }
+        if (cs < (uint32_t)GZX_HEADER + 8 || cs > raw.size() - pos) return SCT_OK;
+        ms.push_back({pos, cs, utotal, us});
+        pos += cs;
+        utotal += us;
+    }
+    if (ms.empty()) return SCT_OK;
+    out.resize(utotal);
+    std::atomic<size_t> next{0};
+    std::atomic<int> bad{0};
+    HostPool pool(std::max(1, std::min<int>(threads, 64)));
+    pool.run([&](int) {
+        for (;;) {
+            const size_t k = next.fetch_add(1);
+            if (k >= ms.size() || bad.load()) break;
+            z_stream z;
+            memset(&z, 0, sizeof z);
+            if (inflateInit2(&z, 15 + 16) != Z_OK) {
+                bad = 1;
+                break;
+            }
+            z.next_in = raw.data() + ms[k].at;
+            z.avail_in = (uInt)ms[k].csize;
+            z.next_out = out.data() + ms[k].uoff;
+            z.avail_out = (uInt)ms[k].usize;
+            const int r = inflate(&z, Z_FINISH);
+            if (r != Z_STREAM_END || z.avail_out != 0 || z.avail_in != 0) bad = 1;
+            inflateEnd(&z);
+        }
+    });
+    if (bad.load()) {
+        out.clear();
+        return SCT_OK;                                       // sizes lied: let the serial path decide (and report)
+    }
+    *handled = true;
+    return SCT_OK;
+}
+
+int read_input_file(const char *path, bool gz, int threads, std::vector<uint8_t> &out) {
+    if (gz) {
+        bool handled = false;
+        const int rc = read_gz_parallel(path, threads, out, &handled);
+        if (rc != SCT_OK || handled) return rc;
+        out.clear();
+    }
+    return read_whole_file(path, gz, out);
+}
+
+namespace {
 
 // bound(first, last) -> upper bound of the bytes of rows [first, last); emit(first, last, p) -> end pointer, counts rows
 template <class Bound, class Emit>

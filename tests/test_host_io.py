@@ -184,3 +184,31 @@ def test_match_trie_writes_gzip_members_the_reference_reader_accepts(tmp_path):
         assert f.read() == plain
     back = mt.read_long_reads(str(p), 4)          # 5 columns: name, e, n, seg, barcodes -> column 3 = the segment
     assert len(back) == int((res.min_ed >= 0).sum())
+
+
+def test_indexed_gzip_members_parallel_and_mixed_files(tmp_path):
+    """The native writer's gzip members carry their sizes in the header's extra field ("SC"): a file made only of such
+    members is inflated in parallel; as soon as one member is foreign (the reference's writer, plain `gzip`) or a size is
+    wrong, the reader takes the serial zlib path — same rows either way."""
+    n = 50000
+    names = [b"r%d" % i for i in range(n)]
+    seqs = [b"ACGTACGTACGTACGTACGTAC"] * n
+    nb, no = hm.pack(names)
+    rb, ro = hm.pack(seqs)
+    z = np.zeros(n, np.int64)
+    plain = lr.format_rows(lr.Reads(nb, no, rb, ro), (z, z, z, z))
+    ours = lr.format_rows(lr.Reads(nb, no, rb, ro), (z, z, z, z), gzip_level=1, threads=4)
+    assert ours[3] & 4 and ours[12:14] == b"SC"                       # FEXTRA with the size subfield
+    csize = int.from_bytes(ours[16:20], "little")
+    assert ours[csize:csize + 2] == b"\x1f\x8b" and gzip.decompress(ours) == plain
+    foreign = gzip.compress(b"tail\t0\t0\tGGGG\n")
+    broken = bytearray(ours)
+    broken[20] ^= 0x01                                                # wrong uncompressed size in the first member
+    for name, data, extra in (("ours.tsv.gz", ours, 0), ("mixed.tsv.gz", ours + foreign, 1),
+                              ("mixed2.tsv.gz", foreign + ours, 1), ("broken.tsv.gz", bytes(broken), 0)):
+        p = tmp_path / name
+        p.write_bytes(data)
+        got = mt.read_long_reads(str(p), 4)
+        assert len(got) == n + extra
+        segs = _unpack(got.seg_bytes, got.offsets)
+        assert segs.count(b"ACGTACGTACGTACGTACGTAC") == n and (extra == 0 or b"GGGG" in segs)

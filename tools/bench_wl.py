@@ -1,7 +1,8 @@
 """extract_sr_bc_from_lr whitelist search on B200: device-resident kernel time against the HBM roofline, end-to-end
 through Whitelist.count (host buffers in), and the CPU restatement on a sample.   python tools/bench_wl.py [W] [n] [steps]
 Workload: W random 16-mers (default 6.8 M = the size of the 10x 3M-february-2018 whitelist), n segments of 38 bases
-(= 2 + 16 + 20, what extract_lr_bc cuts with --num-bp-after 20), 80 % holding one whitelist barcode or its reverse complement."""
+(= 2 + 16 + 20, what extract_lr_bc cuts with --num-bp-after 20), 80 % holding the barcode of one of 10,000 cells (or its
+reverse complement), the rest random."""
 import json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -17,7 +18,8 @@ lut = np.frombuffer(b"ACGT", np.uint8)
 wm = rng.integers(0, 4, size=(W, 16), dtype=np.uint8)
 wbytes, woff = lut[wm].reshape(-1), np.arange(W + 1, dtype=np.int64) * 16
 seg = rng.integers(0, 4, size=(n, SEG), dtype=np.uint8)
-pick = rng.integers(0, W, n)
+cells = rng.choice(W, size=min(W, 10_000), replace=False)      # a real sample holds thousands of cells, not millions
+pick = cells[rng.integers(0, cells.shape[0], n)]
 has = rng.random(n) < 0.8
 rc = rng.random(n) < 0.5
 core = np.where(rc[:, None], 3 - wm[pick][:, ::-1], wm[pick])
