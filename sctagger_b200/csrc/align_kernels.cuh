@@ -22,6 +22,7 @@
 namespace sct {
 
 constexpr int ALN_THREADS = 128;
+constexpr int ALN_LONG_WORK = 384;        // pass 2: reads with more columns left than this get a warp instead of a thread
 constexpr int ALN_BUCKETS = 1024;        // length buckets of 32 bases; longer reads share the last bucket
 
 struct AlignParams {
@@ -35,6 +36,8 @@ struct AlignParams {
     signed char *strand;                 // '+', '-', 0 = NA
     int *dist;                           // -1 = NA
     int *n_locs;
+    int2 *span;                          // first and last end position at the minimum of the winning adapter (pass 1 -> 2)
+    int *work;                           // columns pass 2 has to scan for the read (its sort key)
     const long long *loc_off;            // exclusive scan of n_locs (pass 2)
     int *locs;
     unsigned long long loc_cap;
@@ -77,6 +80,24 @@ __global__ void __launch_bounds__(256) aln_scatter_kernel(const long long *__res
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     order[atomicAdd(&cursor[len_bucket(off[i + 1] - off[i])], 1u)] = i;
+}
+
+// the same counting sort keyed by an int array (pass 2: columns each read still has to scan)
+__global__ void __launch_bounds__(256) aln_hist_work_kernel(const int *__restrict__ work, int n, unsigned int *__restrict__ hist) {
+    __shared__ unsigned int sh[ALN_BUCKETS];
+    for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) atomicAdd(&sh[len_bucket(work[i])], 1u);
+    __syncthreads();
+    for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x)
+        if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+__global__ void __launch_bounds__(256) aln_scatter_work_kernel(const int *__restrict__ work, int n, unsigned int *__restrict__ cursor,
+                                                               int *__restrict__ order) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    order[atomicAdd(&cursor[len_bucket(work[i])], 1u)] = i;
 }
 
 // ---- Myers column ---------------------------------------------------------------------------------------------------
@@ -136,21 +157,25 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass1_kernel(const AlignParam
     Myers a, b;
     a.init(m);
     b.init(m);
-    int best1 = 1 << 20, best2 = 1 << 20, c1 = 0, c2 = 0;
+    int best1 = 1 << 20, best2 = 1 << 20, c1 = 0, c2 = 0, f1 = 0, l1 = 0, f2 = 0, l2 = 0, j = 0;
     for_each_byte(p.bytes, beg, end, [&](uint32_t ch, long long) {
         const uint2 e = s_peq[ch];
         a.step<false>(e.x, top);
         b.step<false>(e.y, top);
-        if (a.score < best1) { best1 = a.score; c1 = 0; }
-        c1 += a.score == best1;
-        if (b.score < best2) { best2 = b.score; c2 = 0; }
-        c2 += b.score == best2;
+        if (a.score < best1) { best1 = a.score; c1 = 0; f1 = j; }
+        if (a.score == best1) { ++c1; l1 = j; }
+        if (b.score < best2) { best2 = b.score; c2 = 0; f2 = j; }
+        if (b.score == best2) { ++c2; l2 = j; }
+        ++j;
     });
     if (end == beg) best1 = best2 = m;       // edlib: empty target -> distance = query length (both adapters: a tie)
     signed char s = 0;
     int d = -1, nl = 0;
-    if (best1 < best2) { s = '+'; d = best1; nl = c1; }
-    else if (best2 < best1) { s = '-'; d = best2; nl = c2; }
+    int2 span = make_int2(0, -1);
+    if (best1 < best2) { s = '+'; d = best1; nl = c1; span = make_int2(f1, l1); }
+    else if (best2 < best1) { s = '-'; d = best2; nl = c2; span = make_int2(f2, l2); }
+    p.span[r] = span;
+    p.work[r] = nl ? (span.x > 2 * m + 2 ? 2 * m + 2 : span.x) + (span.y - span.x + 1) + (s == '-' ? nl * (m + d) : 0) : 0;
     p.strand[r] = s;
     p.dist[r] = d;
     p.n_locs[r] = nl;
@@ -181,26 +206,87 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass2_kernel(const AlignParam
     if (t >= p.n) return;
     const int r = p.order[t];
     const int nl = p.n_locs[r];
-    if (nl == 0) return;
+    if (nl == 0 || p.work[r] > ALN_LONG_WORK) return;             // long spans: aln_pass2_long_kernel, one warp each
     const long long beg = p.off[r], end = p.off[r + 1];
     const long long out0 = p.loc_off[r];
     if ((unsigned long long)(out0 + nl) > p.loc_cap) return;      // the host grows the buffer and repeats the pass
     const int m = p.m, d = p.dist[r];
     const bool fwd = p.strand[r] == '+';
     const uint32_t top = 1u << (m - 1);
+    // Every location lies in [first, last] (pass 1).  Row i of a semi-global DP column is <= i, so an optimal alignment
+    // of any adapter prefix ends within 2m text characters of its start: an automaton restarted 2m + 2 characters before
+    // `first` reproduces the exact columns from `first` on (and only over-estimates before it), and the scan stops at `last`.
+    const int2 span = p.span[r];
+    const long long from = beg + (span.x > 2 * m + 2 ? span.x - (2 * m + 2) : 0), first = beg + span.x, to = beg + span.y + 1;
     Myers a;
     a.init(m);
     int k = 0;
-    for_each_byte(p.bytes, beg, end, [&](uint32_t ch, long long pos) {
+    for_each_byte(p.bytes, from, to < end ? to : end, [&](uint32_t ch, long long pos) {
         const uint2 e = s_peq[ch];
         a.step<false>(fwd ? e.x : e.y, top);
-        if (a.score == d && k < nl) {
+        if (a.score == d && k < nl && pos >= first) {
             // '+': end position (scTagger.py:185);  '-': start - len(seq) - 1 (scTagger.py:189)
             const long long v = fwd ? (pos - beg) : (leftmost_start(p.bytes, beg, pos, p.rpeq2, m, d) - beg) - (end - beg) - 1;
             p.locs[out0 + k] = (int)v;
             ++k;
         }
     });
+}
+
+// Reads whose span is long (no adapter: equal minima scattered over the whole read) would each be one serial chain of
+// thousands of columns — the floor of the whole pass.  Here a warp takes one such read: every lane scans 1/32 of the span
+// behind its own 2m + 2 warm-up columns (same exactness argument), first counting its locations, then — after a warp
+// prefix sum of the counts — scanning again to write them in order.
+__global__ void __launch_bounds__(ALN_THREADS) aln_pass2_long_kernel(const AlignParams p) {
+    __shared__ uint2 s_peq[256];
+    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) s_peq[i] = p.peq[i];
+    __syncthreads();
+    const int w = (blockIdx.x * ALN_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= p.n) return;
+    const int r = p.order[w];                                     // descending work: the long ones come first
+    const int nl = p.n_locs[r];
+    if (nl == 0 || p.work[r] <= ALN_LONG_WORK) return;
+    const long long beg = p.off[r], end = p.off[r + 1];
+    const long long out0 = p.loc_off[r];
+    if ((unsigned long long)(out0 + nl) > p.loc_cap) return;
+    const int m = p.m, d = p.dist[r];
+    const bool fwd = p.strand[r] == '+';
+    const uint32_t top = 1u << (m - 1);
+    const int2 span = p.span[r];
+    const long long first = beg + span.x, stop = (beg + span.y + 1 < end) ? beg + span.y + 1 : end;
+    const long long piece = (stop - first + 31) / 32;
+    const long long lo = first + piece * lane, hi = (lo + piece < stop) ? lo + piece : stop;     // this lane emits [lo, hi)
+    const long long from = (lo - beg > 2 * m + 2) ? lo - (2 * m + 2) : beg;
+    int cnt = 0;
+    if (lo < hi) {
+        Myers a;
+        a.init(m);
+        for_each_byte(p.bytes, from, hi, [&](uint32_t ch, long long pos) {
+            const uint2 e = s_peq[ch];
+            a.step<false>(fwd ? e.x : e.y, top);
+            cnt += (a.score == d && pos >= lo);
+        });
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    int k = incl - cnt;
+    if (cnt > 0) {
+        Myers a;
+        a.init(m);
+        for_each_byte(p.bytes, from, hi, [&](uint32_t ch, long long pos) {
+            const uint2 e = s_peq[ch];
+            a.step<false>(fwd ? e.x : e.y, top);
+            if (a.score == d && pos >= lo && k < nl) {
+                const long long v = fwd ? (pos - beg) : (leftmost_start(p.bytes, beg, pos, p.rpeq2, m, d) - beg) - (end - beg) - 1;
+                p.locs[out0 + k] = (int)v;
+                ++k;
+            }
+        });
+    }
 }
 
 // ---- exclusive scan of n_locs (int32 -> int64 offsets, n + 1 entries) --------------------------------------------------

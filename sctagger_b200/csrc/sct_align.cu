@@ -20,6 +20,8 @@ struct ASlot {
     long long *d_off = nullptr, *d_locoff = nullptr, *d_bsums = nullptr, *d_total = nullptr;
     unsigned int *d_hist = nullptr;
     int *d_order = nullptr, *d_dist = nullptr, *d_nlocs = nullptr, *d_locs = nullptr;
+    int2 *d_span = nullptr;
+    int *d_work = nullptr;
     signed char *d_strand = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
@@ -47,7 +49,7 @@ void free_aslot(ASlot &s) {
     host_free(s.h_bytes); host_free(s.h_off); host_free(s.h_locoff); host_free(s.h_total); host_free(s.h_strand);
     host_free(s.h_dist); host_free(s.h_locs);
     dev_free(s.d_bytes); dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_bsums); dev_free(s.d_total);
-    dev_free(s.d_hist); dev_free(s.d_order); dev_free(s.d_dist); dev_free(s.d_nlocs); dev_free(s.d_locs);
+    dev_free(s.d_hist); dev_free(s.d_order); dev_free(s.d_dist); dev_free(s.d_nlocs); dev_free(s.d_locs); dev_free(s.d_span); dev_free(s.d_work);
     dev_free(s.d_strand);
     s.cap_reads = s.cap_bytes = s.cap_locs = 0;
 }
@@ -79,7 +81,7 @@ int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes) {
         const int64_t c = std::max<int64_t>(reads, 1024);
         host_free(s.h_off); host_free(s.h_locoff); host_free(s.h_strand); host_free(s.h_dist);
         dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_bsums); dev_free(s.d_order); dev_free(s.d_dist);
-        dev_free(s.d_nlocs); dev_free(s.d_strand);
+        dev_free(s.d_nlocs); dev_free(s.d_strand); dev_free(s.d_span); dev_free(s.d_work);
         s.cap_reads = 0;
         CUDA_TRY(cudaMallocHost(&s.h_off, (size_t)(c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMallocHost(&s.h_locoff, (size_t)(c + 1) * sizeof(long long)));
@@ -91,6 +93,8 @@ int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes) {
         CUDA_TRY(cudaMalloc(&s.d_order, (size_t)c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_dist, (size_t)c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_nlocs, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_span, (size_t)c * sizeof(int2)));
+        CUDA_TRY(cudaMalloc(&s.d_work, (size_t)c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_strand, (size_t)c));
         s.cap_reads = c;
         TRY(ensure_locs(s, c * 2));
@@ -119,6 +123,8 @@ AlignParams make_aparams(sct_align_handle *h, ASlot &s) {
     p.strand = s.d_strand;
     p.dist = s.d_dist;
     p.n_locs = s.d_nlocs;
+    p.span = s.d_span;
+    p.work = s.d_work;
     p.loc_off = s.d_locoff;
     p.locs = s.d_locs;
     p.loc_cap = (unsigned long long)s.cap_locs;
@@ -166,9 +172,17 @@ int enqueue_pass2(sct_align_handle *h, ASlot &s, bool copy_back) {
     CUDA_TRY(cudaEventRecord(s.ev2, s.stream));
     if (total > 0) {
         const AlignParams p = make_aparams(h, s);
-        aln_pass2_kernel<<<((int)s.n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        const int n = (int)s.n;
+        // reads re-ordered by the columns pass 2 still has to scan (most: ~2m + a few; reads without the adapter: the
+        // whole read), so that the 32 reads of a warp finish together
+        CUDA_TRY(cudaMemsetAsync(s.d_hist, 0, ALN_BUCKETS * sizeof(unsigned int), s.stream));
+        aln_hist_work_kernel<<<std::min((n + 255) / 256, 1184), 256, 0, s.stream>>>(s.d_work, n, s.d_hist);
+        aln_bucket_scan_kernel<<<1, ALN_BUCKETS, 0, s.stream>>>(s.d_hist);
+        aln_scatter_work_kernel<<<(n + 255) / 256, 256, 0, s.stream>>>(s.d_work, n, s.d_hist, s.d_order);
+        aln_pass2_long_kernel<<<(n + (ALN_THREADS / 32) - 1) / (ALN_THREADS / 32), ALN_THREADS, 0, s.stream>>>(p);
+        aln_pass2_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
         CUDA_TRY(cudaGetLastError());
-        h->stats[0] += 1;
+        h->stats[0] += 5;
         if (copy_back)
             CUDA_TRY(cudaMemcpyAsync(s.h_locs, s.d_locs, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
     }
