@@ -69,6 +69,34 @@ def test_long_reads_and_length_sorting():
     _same(_lib.align_reads(synth.ADAPTER, rb, off), oracle.align(synth.ADAPTER, rb, off, algo="bv"))
 
 
+def test_long_location_spans_take_the_warp_path():
+    """Reads whose locations are far apart (no adapter at all; the adapter twice, 3 kb apart; a long homopolymer where
+    every position ties) go through aln_pass2_long_kernel (one warp per read, span split over the lanes); reads with a
+    span of a few columns stay on the thread-per-read kernel.  Both against the oracle, both strands."""
+    rng = np.random.default_rng(21)
+    lut = np.frombuffer(b"ACGT", np.uint8)
+    a1 = synth.ADAPTER
+    rc = bytes({65: 84, 67: 71, 71: 67, 84: 65}[c] for c in reversed(a1))
+    rand = lambda n: lut[rng.integers(0, 4, n)].tobytes()
+    reads = []
+    for i in range(200):
+        k = i % 5
+        if k == 0:
+            reads.append(rand(int(rng.integers(500, 5000))))                              # no adapter
+        elif k == 1:
+            reads.append(rand(40) + a1 + rand(3000) + a1 + rand(int(rng.integers(0, 50))))   # '+' twice, far apart
+        elif k == 2:
+            reads.append(rand(30) + rc + rand(2500) + rc + rand(20))                      # '-' twice: two start searches
+        elif k == 3:
+            reads.append(b"T" * int(rng.integers(400, 3000)))                             # every column ties
+        else:
+            reads.append(rand(20) + a1 + rand(int(rng.integers(100, 2000))))              # short span
+    rb, off = _pack(reads)
+    got = _lib.align_reads(a1, rb, off)
+    _same(got, oracle.align(a1, rb, off))
+    assert int(np.diff(got[2]).max()) > 300                                               # the homopolymer reads
+
+
 def test_align_errors():
     with pytest.raises(_lib.SctError) as e:
         _lib.Aligner(b"A" * 33)
