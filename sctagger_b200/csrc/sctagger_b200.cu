@@ -66,6 +66,7 @@ struct sct_handle {
     int tie_per_seg = 8;
     int seed_ctas_per_sm = 6;
     int64_t n_pass = 0;
+    bool seed_pre_ok = false;
     uint32_t *d_ovf_scratch = nullptr;
     int ovf_blocks = 16, ovf_cap = 0;
     uint8_t *d_flush = nullptr;
@@ -506,16 +507,19 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
             h->seed_ok = h->clean_barcodes && P <= SEED_MAX_PIECES && min_len >= 4 && B > 0 &&
                          (size_t)P * B < ((size_t)1 << 23);          // entry index shares a word with position / piece / strand
             // anchored pre-check (seed_precheck): per piece the side of the barcode with more characters left
+            bool pre_ok = true;
             for (int q = 0; q < P && q < SEED_MAX_PIECES; ++q) {
                 const int po = h->seed.piece_off[q], ln = h->seed.piece_len[q];
                 const int right = bl - (po + ln), left = po;
                 const bool go_left = left > right;
                 const int avail = go_left ? left : right;
-                const int pairs = std::min(avail / 2, max_error >= 3 ? 4 : 3);
+                const int pairs = seed_pre_pairs(max_error);
+                if (avail < 2 * pairs) pre_ok = false;
                 h->seed.pre[q] = (uint32_t)(go_left ? bl - po : po + ln) | ((go_left ? 1u : 0u) << 5) |
                                  ((uint32_t)pairs << 6) | ((uint32_t)ln << 9);
             }
-            h->seed.prefilter = (bl == 16) ? 1 : 0;
+            h->seed.prefilter = (bl == 16 && pre_ok) ? 1 : 0;
+            h->seed_pre_ok = h->seed.prefilter != 0;
             if (h->seed_ok) {
                 std::vector<uint32_t> boff(boff_words, 0u), ew((size_t)P * B), ei((size_t)P * B), code((size_t)B);
                 for (int b = 0; b < B; ++b) {
@@ -607,7 +611,8 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
             return fail(SCT_E_UNSUPPORTED, "the tile kernel needs ACGT-only barcodes and a table that fits shared memory");
         h->path_override = (int)value;
     } else if (k == "seed_prefilter") {
-        h->seed.prefilter = (value != 0 && h->bl == 16) ? 1 : 0;
+        if (value != 0 && !h->seed_pre_ok) return fail(SCT_E_ARG, "seed_prefilter is not available for this barcode length / -mr");
+        h->seed.prefilter = value != 0 ? 1 : 0;
     } else if (k == "seed_ctas_per_sm") {
         if (value < 1 || value > 32) return fail(SCT_E_ARG, "seed_ctas_per_sm must be 1..32");
         h->seed_ctas_per_sm = (int)value;

@@ -46,6 +46,7 @@ struct SeedIndex {
     uint32_t pre[SEED_MAX_PIECES];
     int prefilter;                         // 1 = run the anchored pre-check (option "seed_prefilter")
 };
+__host__ __device__ constexpr int seed_pre_pairs(int K) { return K >= 3 ? 4 : 3; }   // 6 characters; 8 at -mr 3
 constexpr int SEED_QUEUE_CAP = 64;         // pre-check survivors waiting for a full verification, per warp
 
 __device__ __forceinline__ uint32_t mul_rt(uint32_t x, uint32_t m) {
@@ -124,8 +125,6 @@ __device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t tab_a
 template <int K>
 __device__ __forceinline__ bool seed_precheck(uint32_t word, uint32_t pre, int j, int n, uint32_t pair_a, uint32_t strand,
                                               uint32_t full, uint32_t two) {
-    const int pairs = (pre >> 6) & 7;
-    if (pairs == 0) return true;
     const uint32_t left = (pre >> 5) & 1u;
     uint32_t rcw = __brev(~word);
     rcw = ((rcw & 0x55555555u) << 1) | ((rcw >> 1) & 0x55555555u);
@@ -156,16 +155,15 @@ __device__ __forceinline__ bool seed_precheck(uint32_t word, uint32_t pre, int j
             S[d] = s;
         }
     };
-    constexpr int MAXP = K >= 3 ? 4 : 3;                   // sct_create never asks for more pairs than this
+    // SEED_PRE_PAIRS(K) pair lookups for every piece: sct_create switches the pre-check off when a piece has fewer
+    // characters beside it
 #pragma unroll
-    for (int m = 0; m < MAXP; ++m) {
-        if (m < pairs) {
-            const uint32_t sh = m == 0 ? (w << 3) : (w >> (4 * m - 3));
-            uint32_t e0, e1;
-            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(e0), "=r"(e1) : "r"(and_or(sh, 0x78u, tab_a)));
-            row(e0);
-            row(e1);
-        }
+    for (int m = 0; m < seed_pre_pairs(K); ++m) {
+        const uint32_t sh = m == 0 ? (w << 3) : (w >> (4 * m - 3));
+        uint32_t e0, e1;
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(e0), "=r"(e1) : "r"(and_or(sh, 0x78u, tab_a)));
+        row(e0);
+        row(e1);
     }
     return (R[K] & full) != 0u;
 }
