@@ -41,7 +41,6 @@ struct Counters {                    // device-side cursors, zeroed before every
     unsigned int cur_fast, cur_gen, cur_ovf, cur_dp;
     unsigned long long tie_cursor;   // bump allocator over tie_buf (may run past tie_cap: the pass is then redone)
     unsigned long long n_cand;       // seeded kernel: candidates generated (statistics)
-    unsigned long long n_pass;       // seeded kernel: candidates that passed the anchored pre-check and were fully verified
 };
 
 struct MatchParams {

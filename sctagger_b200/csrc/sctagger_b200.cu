@@ -56,7 +56,8 @@ struct sct_handle {
     int n_tiles = 0;
     bool clean_barcodes = true, use_dp = false, fast_ok = false, seed_ok = false;
     int path_override = 0;       // 0 auto, 1 force generic, 2 force dp, 3 force the tile (all-pairs) kernel
-    uint32_t *d_boff = nullptr, *d_ewords = nullptr, *d_eids = nullptr;
+    uint32_t *d_boff = nullptr, *d_eids = nullptr;
+    uint2 *d_ewords = nullptr;
     SeedIndex seed{};
     size_t fast_smem = 0;
     int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
@@ -65,7 +66,6 @@ struct sct_handle {
     HostPool *pool = nullptr;
     int tie_per_seg = 8;
     int seed_ctas_per_sm = 6;
-    int64_t n_pass = 0;
     bool seed_pre_ok = false;
     uint32_t *d_ovf_scratch = nullptr;
     int ovf_blocks = 16, ovf_cap = 0;
@@ -190,8 +190,9 @@ int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 non
     if (fast == 2) {
         // seeded kernel: small static shared memory, many resident warps (latency-bound gathers + verification)
         const int grid = h->sm_count * h->seed_ctas_per_sm;
-        if (h->bl == 16) match_seed_kernel<K, true><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
-        else match_seed_kernel<K, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
+        if (h->bl == 16 && h->seed.prefilter) match_seed_kernel<K, true, true><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
+        else if (h->bl == 16) match_seed_kernel<K, true, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
+        else match_seed_kernel<K, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
         CUDA_TRY(cudaGetLastError());
         CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
     } else if (fast == 1) {
@@ -298,8 +299,6 @@ int complete_pass(sct_handle *h, Slot &s) {
             h->stats[2] += s.h_ctr->n_gen + s.h_ctr->n_ovf;
             h->stats[6] += s.h_ctr->n_dp;
             h->stats[7] += (int64_t)s.h_ctr->n_cand;
-            h->n_pass += (int64_t)s.h_ctr->n_pass;
-            if (g_tr.on) fprintf(stderr, "[sct] seeded kernel: %llu candidates, %llu passed the pre-check\n", s.h_ctr->n_cand, s.h_ctr->n_pass);
             return SCT_OK;
         }
         const unsigned long long need = s.h_ctr->tie_cursor + 4096;
@@ -521,11 +520,15 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
             h->seed.prefilter = (bl == 16 && pre_ok) ? 1 : 0;
             h->seed_pre_ok = h->seed.prefilter != 0;
             if (h->seed_ok) {
-                std::vector<uint32_t> boff(boff_words, 0u), ew((size_t)P * B), ei((size_t)P * B), code((size_t)B);
+                std::vector<uint32_t> boff(boff_words, 0u), ei((size_t)P * B), code((size_t)B), rcode((size_t)B);
+                std::vector<uint2> ew((size_t)P * B);
                 for (int b = 0; b < B; ++b) {
                     uint32_t w = 0;
                     for (int i = 0; i < bl; ++i) w |= (uint32_t)patF[(size_t)b * bl + i] << (2 * i);
                     code[b] = w;
+                    uint32_t rw = 0;                         // reverse complement, same packing (meaningful for bl = 16)
+                    for (int i = 0; i < bl; ++i) rw |= (uint32_t)(3 - patF[(size_t)b * bl + (bl - 1 - i)]) << (2 * i);
+                    rcode[b] = rw;
                 }
                 for (int q = 0; q < P; ++q) {
                     const int po = h->seed.piece_off[q], ln = h->seed.piece_len[q];
@@ -538,15 +541,15 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
                     std::vector<uint32_t> cur(bo, bo + nb);
                     for (int b = 0; b < B; ++b) {            // ascending barcode id inside a bucket
                         const uint32_t at = cur[(code[b] >> (2 * po)) & mask]++;
-                        ew[at] = code[b];
+                        ew[at] = make_uint2(code[b], rcode[b]);
                         ei[at] = (uint32_t)b;
                     }
                 }
                 CUDA_TRY(cudaMalloc(&h->d_boff, boff.size() * 4));
-                CUDA_TRY(cudaMalloc(&h->d_ewords, ew.size() * 4));
+                CUDA_TRY(cudaMalloc(&h->d_ewords, ew.size() * sizeof(uint2)));
                 CUDA_TRY(cudaMalloc(&h->d_eids, ei.size() * 4));
                 CUDA_TRY(cudaMemcpy(h->d_boff, boff.data(), boff.size() * 4, cudaMemcpyHostToDevice));
-                CUDA_TRY(cudaMemcpy(h->d_ewords, ew.data(), ew.size() * 4, cudaMemcpyHostToDevice));
+                CUDA_TRY(cudaMemcpy(h->d_ewords, ew.data(), ew.size() * sizeof(uint2), cudaMemcpyHostToDevice));
                 CUDA_TRY(cudaMemcpy(h->d_eids, ei.data(), ei.size() * 4, cudaMemcpyHostToDevice));
                 h->seed.boff = h->d_boff;
                 h->seed.ewords = h->d_ewords;

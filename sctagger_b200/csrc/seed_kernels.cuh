@@ -34,7 +34,8 @@ constexpr int SEED_MAX_PIECES = 4;
 
 struct SeedIndex {
     const uint32_t *boff;                  // per piece: 4^len + 1 absolute entry offsets, pieces concatenated
-    const uint32_t *ewords;                // entries: barcode as 2-bit codes, character i at bits 2i..2i+1
+    const uint2 *ewords;                   // entries: .x = barcode as 2-bit codes (character i at bits 2i..2i+1),
+                                           //          .y = its reverse complement in the same packing (bl = 16 only)
     const uint32_t *eids;                  // entries: barcode index
     int n_pieces;
     int piece_off[SEED_MAX_PIECES];        // offset of the piece in the barcode
@@ -123,20 +124,17 @@ __device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t tab_a
 // surviving pieces (pigeonhole), and that candidate passes.  Measured at -mr 2: 89.8 % of the candidates stop here, at
 // ~100 of the loop's 175 instructions per 32 candidates (a full verification is ~175 more).
 template <int K>
-__device__ __forceinline__ bool seed_precheck(uint32_t word, uint32_t pre, int j, int n, uint32_t pair_a, uint32_t strand,
-                                              uint32_t full, uint32_t two) {
+__device__ __forceinline__ bool seed_precheck(uint2 words, uint32_t pre, int j, int n, uint32_t pair_a, uint32_t strand,
+                                              uint32_t full, uint32_t two, uint32_t init_a) {
     const uint32_t left = (pre >> 5) & 1u;
-    uint32_t rcw = __brev(~word);
-    rcw = ((rcw & 0x55555555u) << 1) | ((rcw >> 1) & 0x55555555u);
-    const uint32_t w = (left ? rcw : word) >> (2 * (pre & 31u));
+    const uint32_t w = (left ? words.y : words.x) >> (2 * (pre & 31u));
     const uint32_t tab_a = pair_a + (strand ^ left) * 128u;
     const int b0 = left ? n - j : j + (int)((pre >> 9) & 31u);
-    uint32_t R[K + 1], S[K + 1];
-#pragma unroll
-    for (int d = 0; d <= K; ++d) {
-        R[d] = ((2u << d) - 1u) << b0;
-        S[d] = R[d] << 1;
-    }
+    // start state of level d = bits b0 .. b0+d, from a per-CTA table indexed by b0: {R0, S0, R1, S1}, {R2, S2, R3, S3}
+    uint32_t R[4], S[4];
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(S[0]), "=r"(R[1]), "=r"(S[1]) : "r"(init_a + 32u * (uint32_t)b0));
+    if (K >= 2)
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[2]), "=r"(S[2]), "=r"(R[3]), "=r"(S[3]) : "r"(init_a + 32u * (uint32_t)b0 + 16u));
     auto row = [&](uint32_t eq) {
         uint32_t r = S[0] & eq;
         uint32_t s = mul_rt(r, two);
@@ -198,7 +196,7 @@ __device__ __forceinline__ int sort_unique(uint32_t *list, uint32_t *tmp, int co
     return out;
 }
 
-template <int K, bool BL16>
+template <int K, bool BL16, bool PRE>
 __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchParams p, const SeedIndex ix,
                                                                   const unsigned long long *__restrict__ pk) {
     constexpr int NSLOT = 2 * (K + 1) * 32;
@@ -210,20 +208,31 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
     __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
     __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
     __shared__ uint32_t s_pre[SEED_MAX_PIECES];                // ix.pre (indexed per candidate: not from the parameter bank)
+    __shared__ __align__(16) uint32_t s_init[33][8];           // pre-check start states by boundary: R0 S0 R1 S1 R2 S2 R3 S3
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x < SEED_MAX_PIECES) {
         const uint32_t t = threadIdx.x;
         s_pre[t] = t == 0 ? ix.pre[0] : t == 1 ? ix.pre[1] : t == 2 ? ix.pre[2] : ix.pre[3];
     }
+    if (threadIdx.x < 33) {
+        const uint32_t b = threadIdx.x;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            const uint32_t r = b < 32 ? (((2u << d) - 1u) << b) : 0u;
+            s_init[b][2 * d] = r;
+            s_init[b][2 * d + 1] = r << 1;
+        }
+    }
     __syncthreads();
+    const uint32_t init_a = smem_u32(&s_init[0][0]);
     uint32_t *prefix = s_prefix[warp], *start = s_start[warp], *list = s_list[warp], *tmp = s_tmp[warp];
     const uint32_t pair_a = smem_u32(&s_pair[warp][0][0]);
     const unsigned int n_fast = p.ctr->n_fast;
     const int bl = p.bl;
     const int P = ix.n_pieces;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    unsigned long long n_cand = 0, n_pass = 0;
+    unsigned long long n_cand = 0;
 
     for (;;) {
         unsigned int idx = 0;
@@ -297,7 +306,7 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
             int level = K + 1;
             const uint32_t entry = item & 0x7FFFFFFFu, strand = item >> 31;
             if (valid) {
-                const uint32_t word = __ldg(ix.ewords + entry);
+                const uint32_t word = __ldg(&ix.ewords[entry].x);
                 level = seed_verify<K, BL16>(word, bl, pair_a + strand * 128u, full, ix.two);
             }
             const unsigned hit = __ballot_sync(FULL, level <= K);
@@ -335,16 +344,15 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
                 const uint32_t entry = (sw & 0x7FFFFFu) + (me - prefix[pos]);
                 item = entry | (strand << 31);
                 pass = true;
-                if (BL16 && ix.prefilter) {
-                    const uint32_t word = __ldg(ix.ewords + entry);
-                    pass = seed_precheck<K>(word, s_pre[(sw >> 28) & 3u], (int)((sw >> 23) & 31u), n, pair_a, strand,
-                                            full, ix.two);
+                if (BL16 && PRE) {
+                    const uint2 words = __ldg(ix.ewords + entry);
+                    pass = seed_precheck<K>(words, s_pre[(sw >> 28) & 3u], (int)((sw >> 23) & 31u), n, pair_a, strand,
+                                            full, ix.two, init_a);
                 }
             }
             const unsigned pm = __ballot_sync(FULL, pass);
             if (pass) queue[qn + __popc(pm & lt_mask)] = item;
             qn += __popc(pm);
-            n_pass += __popc(pm);
             __syncwarp();
             if (qn >= 32) {
                 verify(queue[lane], true);
@@ -363,7 +371,6 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
     }
     if (lane == 0 && n_cand) {
         atomicAdd(&p.ctr->n_cand, n_cand);
-        atomicAdd(&p.ctr->n_pass, n_pass);
     }
 }
 
