@@ -12,7 +12,7 @@ its own batch of the same shape (reads shard, the barcode table is replicated; n
   e2e        the same metric through the public host call (Matcher.match -> sct_match): HOST numpy buffers in, HOST
              result arrays out, every step; pinned staging, H2D and D2H are inside the timed region (wall clock between
              barrier + synchronize on both sides, max over ranks).
-  roofline   the dominant kernel (match_fast_kernel) against the INT32 ALU issue rate: algorithmic lane-ops
+  roofline   the dominant kernel (match_seed_kernel) against the INT32 ALU issue rate: algorithmic lane-ops
              (14 per Myers column update x 2B x sum(len)) / kernel time (CUDA events) / the LOP3 issue
              peak measured live on this GPU (sct_measure_int32_peak).  HBM figures are reported as the minor counter.
   cpu_baseline / --impl reference   the CPU port of the reference's trie algorithm (oracle/trie_oracle.c, OpenMP over
