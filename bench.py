@@ -181,9 +181,9 @@ def cpu_arm(barcodes, n_sample, max_error, seed, repeats=1):
 
 
 def run_reference(a, rank):
-    """--impl reference: the CPU arm alone, rank 0 only (other ranks exit 0 without work)."""
+    """--impl reference: the CPU arm alone, rank 0 only (other ranks exit 0 without work).  -> the JSON line"""
     if rank != 0:
-        return
+        return None
     from sctagger_b200 import synth
     bc = synth.make_barcodes(a.barcodes, synth.SEEDS["cfg2"])
     n = min(CPU_SAMPLE, a.segments)
@@ -196,7 +196,7 @@ def run_reference(a, rank):
         t += dt
     v = n * a.steps / t
     sample = f"{n:,} of the workload's {a.segments:,} segments per step x {a.barcodes:,} barcodes, -t {cores}"
-    print(json.dumps({
+    return json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": 1e3 * t / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
@@ -207,17 +207,32 @@ def run_reference(a, rank):
         "note": "CPU port (oracle/trie_oracle.c) of the reference's trie build + error-bounded DFS, one OpenMP thread "
                 "per core over the reference's own prefix tasks; the reference itself is a Python script that is not "
                 "present on the GPU box (its measured throughput in the build container is in BASELINE.md)",
-    }), flush=True)
+    })
 
 
 def main():
+    # everything but the one JSON line goes to STDERR, also what libraries write to file descriptor 1 themselves
+    # (NCCL prints its version banner there when NCCL_DEBUG is set on the box)
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        line = _main()
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
+    if line is not None:
+        print(line, flush=True)
+
+
+def _main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if a.impl == "reference":
-        run_reference(a, rank)
-        return
+        return run_reference(a, rank)
 
     import torch
     import torch.distributed as dist
@@ -317,6 +332,7 @@ def main():
                     "source": f"profiles/r01_ncu_match_seed_K{a.max_error}.txt"}
     m.close()
 
+    out = None
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -354,10 +370,11 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{min(CPU_SAMPLE, n):,} segments of the same generator x {a.barcodes:,} "
                                               f"barcodes, {dt:.1f} s, oracle/trie_oracle.c with -t {cores}"}
-        print(json.dumps(line), flush=True)
+        out = json.dumps(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    return out
 
 
 def _ncu_profile(name):
