@@ -225,7 +225,10 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
         }
     }
     __syncthreads();
-    const uint32_t init_a = smem_u32(&s_init[0][0]);
+    // opaque copies: ptxas otherwise re-derives these shared-memory addresses from SR_CgaCtaId in every loop iteration
+    uint32_t init_a = smem_u32(&s_init[0][0]), pre_a = smem_u32(&s_pre[0]);
+    asm volatile("mov.u32 %0, %0;" : "+r"(init_a));
+    asm volatile("mov.u32 %0, %0;" : "+r"(pre_a));
     uint32_t *prefix = s_prefix[warp], *start = s_start[warp], *list = s_list[warp], *tmp = s_tmp[warp];
     const uint32_t pair_a = smem_u32(&s_pair[warp][0][0]);
     const unsigned int n_fast = p.ctr->n_fast;
@@ -346,8 +349,9 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
                 pass = true;
                 if (BL16 && PRE) {
                     const uint2 words = __ldg(ix.ewords + entry);
-                    pass = seed_precheck<K>(words, s_pre[(sw >> 28) & 3u], (int)((sw >> 23) & 31u), n, pair_a, strand,
-                                            full, ix.two, init_a);
+                    uint32_t pre;
+                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(pre) : "r"(pre_a + ((sw >> 26) & 12u)));
+                    pass = seed_precheck<K>(words, pre, (int)((sw >> 23) & 31u), n, pair_a, strand, full, ix.two, init_a);
                 }
             }
             const unsigned pm = __ballot_sync(FULL, pass);
