@@ -217,6 +217,22 @@ def test_baseline_config_10m_chunked_streaming_is_shard_invariant():
     assert int((parts[0].min_ed >= 0).sum()) == 887_994
 
 
+def test_cuda_path_matches_the_reference_digest_at_100k_x_25k():
+    """Same digest as tests/test_oracle.py::test_oracle_matches_the_reference_digest_at_100k_x_25k, through the CUDA path:
+    the unmodified reference's output at the headline table size (25,000 barcodes), byte for byte."""
+    import hashlib
+    import json
+    import os
+    meta = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref100k.json")))
+    bc = synth.make_barcodes(meta["barcodes"], meta["barcode_seed"])
+    sb, off = synth.make_segments(bc, meta["segments"], meta["segment_seed"])
+    res = _lib.match_segments(bc, sb, off, max_error=meta["max_error"], threads=meta["threads"])
+    nb, no = synth.read_names(meta["segments"])
+    data = mt.format_reads_rows(mt.LongReads(nb, no, sb, off), res, [bytes(b).decode() for b in bc])
+    assert data.count(b"\n") == meta["rows"]
+    assert hashlib.sha256(data).hexdigest() == meta["sha256"]
+
+
 def test_error_codes():
     bc = synth.make_barcodes(10, 1)
     with pytest.raises(_lib.SctError) as e:
