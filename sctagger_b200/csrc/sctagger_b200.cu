@@ -504,7 +504,7 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
             }
             // below 4 characters per piece nearly every barcode is a candidate: the all-pairs tile kernel is faster there
             h->seed_ok = h->clean_barcodes && P <= SEED_MAX_PIECES && min_len >= 4 && B > 0 &&
-                         (size_t)P * B < ((size_t)1 << 23);          // entry index shares a word with position / piece / strand
+                         (size_t)P * B < ((size_t)1 << 31);          // entry index shares a word with the strand bit
             // anchored pre-check (seed_precheck): per piece the side of the barcode with more characters left
             bool pre_ok = true;
             for (int q = 0; q < P && q < SEED_MAX_PIECES; ++q) {

@@ -124,17 +124,18 @@ __device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t tab_a
 // surviving pieces (pigeonhole), and that candidate passes.  Measured at -mr 2: 89.8 % of the candidates stop here, at
 // ~100 of the loop's 175 instructions per 32 candidates (a full verification is ~175 more).
 template <int K>
-__device__ __forceinline__ bool seed_precheck(uint2 words, uint32_t pre, int j, int n, uint32_t pair_a, uint32_t strand,
-                                              uint32_t full, uint32_t two, uint32_t init_a) {
-    const uint32_t left = (pre >> 5) & 1u;
-    const uint32_t w = (left ? words.y : words.x) >> (2 * (pre & 31u));
-    const uint32_t tab_a = pair_a + (strand ^ left) * 128u;
-    const int b0 = left ? n - j : j + (int)((pre >> 9) & 31u);
+// aux (per slot, built once per segment): bits 0-5 = right shift of the barcode word, bit 6 = extend left (use the
+// reverse-complemented word), bit 7 = which strand's pair table, bits 16-31 = byte offset of the start states (32 * b0)
+__device__ __forceinline__ bool seed_precheck(uint2 words, uint32_t aux, uint32_t pair_a, uint32_t full, uint32_t two,
+                                              uint32_t init_a) {
+    const uint32_t w = ((aux & 64u) ? words.y : words.x) >> (aux & 63u);
+    const uint32_t tab_a = pair_a + (aux & 128u);
+    const uint32_t st_a = init_a + (aux >> 16);
     // start state of level d = bits b0 .. b0+d, from a per-CTA table indexed by b0: {R0, S0, R1, S1}, {R2, S2, R3, S3}
     uint32_t R[4], S[4];
-    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(S[0]), "=r"(R[1]), "=r"(S[1]) : "r"(init_a + 32u * (uint32_t)b0));
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(S[0]), "=r"(R[1]), "=r"(S[1]) : "r"(st_a));
     if (K >= 2)
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[2]), "=r"(S[2]), "=r"(R[3]), "=r"(S[3]) : "r"(init_a + 32u * (uint32_t)b0 + 16u));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[2]), "=r"(S[2]), "=r"(R[3]), "=r"(S[3]) : "r"(st_a + 16u));
     auto row = [&](uint32_t eq) {
         uint32_t r = S[0] & eq;
         uint32_t s = mul_rt(r, two);
@@ -202,19 +203,15 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
     constexpr int NSLOT = 2 * (K + 1) * 32;
     // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
     __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
-    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket | position << 23 | piece << 28 | strand << 31
+    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket | strand << 31
+    __shared__ uint32_t s_aux[SEED_WARPS][PRE ? NSLOT : 1];    // pre-check operands of the slot (see seed_precheck)
     __shared__ uint32_t s_queue[SEED_WARPS][SEED_QUEUE_CAP];   // pre-check survivors: entry | strand << 31
     __shared__ __align__(128) uint2 s_pair[SEED_WARPS][2][16]; // per strand: entry c0 | c1 << 2 = {Eq[c0], Eq[c1]}
     __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
     __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
-    __shared__ uint32_t s_pre[SEED_MAX_PIECES];                // ix.pre (indexed per candidate: not from the parameter bank)
     __shared__ __align__(16) uint32_t s_init[33][8];           // pre-check start states by boundary: R0 S0 R1 S1 R2 S2 R3 S3
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    if (threadIdx.x < SEED_MAX_PIECES) {
-        const uint32_t t = threadIdx.x;
-        s_pre[t] = t == 0 ? ix.pre[0] : t == 1 ? ix.pre[1] : t == 2 ? ix.pre[2] : ix.pre[3];
-    }
     if (threadIdx.x < 33) {
         const uint32_t b = threadIdx.x;
 #pragma unroll
@@ -226,9 +223,8 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
     }
     __syncthreads();
     // opaque copies: ptxas otherwise re-derives these shared-memory addresses from SR_CgaCtaId in every loop iteration
-    uint32_t init_a = smem_u32(&s_init[0][0]), pre_a = smem_u32(&s_pre[0]);
+    uint32_t init_a = smem_u32(&s_init[0][0]);
     asm volatile("mov.u32 %0, %0;" : "+r"(init_a));
-    asm volatile("mov.u32 %0, %0;" : "+r"(pre_a));
     uint32_t *prefix = s_prefix[warp], *start = s_start[warp], *list = s_list[warp], *tmp = s_tmp[warp];
     const uint32_t pair_a = smem_u32(&s_pair[warp][0][0]);
     const unsigned int n_fast = p.ctr->n_fast;
@@ -293,7 +289,12 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
                 if (len) {
                     const int slot = n_slots + __popc(live & lt_mask);
                     prefix[slot] = total + incl - len;
-                    start[slot] = st | ((uint32_t)lane << 23) | ((uint32_t)q << 28) | ((uint32_t)s << 31);
+                    start[slot] = st | ((uint32_t)s << 31);
+                    if (PRE) {
+                        const uint32_t pre = ix.pre[q], left = (pre >> 5) & 1u;
+                        const uint32_t b0 = left ? (uint32_t)(n - lane) : (uint32_t)lane + ((pre >> 9) & 31u);
+                        s_aux[warp][slot] = (2u * (pre & 31u)) | (left << 6) | ((((uint32_t)s) ^ left) << 7) | (b0 << 21);
+                    }
                 }
                 n_slots += __popc(live);
                 total += __shfl_sync(FULL, incl, 31);
@@ -344,14 +345,12 @@ __global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchPar
             if (me < total) {
                 const uint32_t sw = start[pos];
                 const uint32_t strand = sw >> 31;
-                const uint32_t entry = (sw & 0x7FFFFFu) + (me - prefix[pos]);
+                const uint32_t entry = (sw & 0x7FFFFFFFu) + (me - prefix[pos]);
                 item = entry | (strand << 31);
                 pass = true;
                 if (BL16 && PRE) {
                     const uint2 words = __ldg(ix.ewords + entry);
-                    uint32_t pre;
-                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(pre) : "r"(pre_a + ((sw >> 26) & 12u)));
-                    pass = seed_precheck<K>(words, pre, (int)((sw >> 23) & 31u), n, pair_a, strand, full, ix.two, init_a);
+                    pass = seed_precheck<K>(words, s_aux[warp][pos], pair_a, full, ix.two, init_a);
                 }
             }
             const unsigned pm = __ballot_sync(FULL, pass);

@@ -217,13 +217,14 @@ def test_baseline_config_10m_chunked_streaming_is_shard_invariant():
     assert int((parts[0].min_ed >= 0).sum()) == 887_994
 
 
-def test_cuda_path_matches_the_reference_digest_at_100k_x_25k():
+@pytest.mark.parametrize("name", ["ref100k.json", "ref10k_mr3.json"])
+def test_cuda_path_matches_the_reference_digest_at_100k_x_25k(name):
     """Same digest as tests/test_oracle.py::test_oracle_matches_the_reference_digest_at_100k_x_25k, through the CUDA path:
     the unmodified reference's output at the headline table size (25,000 barcodes), byte for byte."""
     import hashlib
     import json
     import os
-    meta = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref100k.json")))
+    meta = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name)))
     bc = synth.make_barcodes(meta["barcodes"], meta["barcode_seed"])
     sb, off = synth.make_segments(bc, meta["segments"], meta["segment_seed"])
     res = _lib.match_segments(bc, sb, off, max_error=meta["max_error"], threads=meta["threads"])

@@ -12,6 +12,9 @@ sys.path.insert(0, ROOT)
 from sctagger_b200 import synth  # noqa: E402
 
 N, B, MR, T = 100_000, 25_000, 2, 8
+NAME = "ref100k.json"
+if len(sys.argv) > 3:      # python tools/make_golden_100k.py <segments> <max_error> <file name under tests/golden>
+    N, MR, NAME = int(sys.argv[1]), int(sys.argv[2]), sys.argv[3]
 with tempfile.TemporaryDirectory() as d:
     bc = synth.make_barcodes(B, synth.SEEDS["cfg2"])
     sb, off = synth.make_segments(bc, N, 2002)
@@ -28,5 +31,5 @@ meta = {"segments": N, "barcodes": B, "max_error": MR, "threads": T, "barcode_se
         "rows": len(rows) - 1, "bytes": len(data), "sha256": hashlib.sha256(data).hexdigest(),
         "first_rows": [r.decode() for r in rows[:3]], "reference_seconds": round(secs, 1), "host_cores": os.cpu_count(),
         "generator": "tools/make_golden_100k.py"}
-json.dump(meta, open(os.path.join(ROOT, "tests", "golden", "ref100k.json"), "w"), indent=1)
+json.dump(meta, open(os.path.join(ROOT, "tests", "golden", NAME), "w"), indent=1)
 print(json.dumps(meta))
