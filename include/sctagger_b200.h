@@ -102,6 +102,7 @@ int sct_stats(sct_handle *h, int64_t stats[8]);
  *                                         generic bit-parallel kernel, 2 = force the DP kernel, 3 = use the all-pairs tile
  *                                         kernel instead of the seeded one
  *   "seed_ctas_per_sm"                    resident CTAs per SM of the seeded kernel (grid = SMs x this)
+ *   "seed_prefilter"                      0 = verify every seeded candidate in full (no anchored pre-check); same results
  */
 int sct_set_option(sct_handle *h, const char *key, int64_t value);
 
