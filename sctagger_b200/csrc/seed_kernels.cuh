@@ -198,7 +198,7 @@ __device__ __forceinline__ int sort_unique(uint32_t *list, uint32_t *tmp, int co
 }
 
 template <int K, bool BL16, bool PRE>
-__global__ void __launch_bounds__(SEED_THREADS) match_seed_kernel(const MatchParams p, const SeedIndex ix,
+__global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const MatchParams p, const SeedIndex ix,
                                                                   const unsigned long long *__restrict__ pk) {
     constexpr int NSLOT = 2 * (K + 1) * 32;
     // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
