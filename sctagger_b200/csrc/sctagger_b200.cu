@@ -521,7 +521,7 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
             h->seed_pre_ok = h->seed.prefilter != 0;
             if (h->seed_ok) {
                 std::vector<uint32_t> boff(boff_words, 0u), ei((size_t)P * B), code((size_t)B), rcode((size_t)B);
-                std::vector<uint2> ew((size_t)P * B);
+                std::vector<uint2> ew((size_t)P * B + 32, make_uint2(0u, 0u));   // + 32: the kernel's branch-free tail reads past the last bucket
                 for (int b = 0; b < B; ++b) {
                     uint32_t w = 0;
                     for (int i = 0; i < bl; ++i) w |= (uint32_t)patF[(size_t)b * bl + i] << (2 * i);

@@ -340,18 +340,14 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
             const int pos = cur + __popc(heads & lt_mask);
             cur += __popc(heads);
             const uint32_t me = t0 + lane;
-            bool pass = false;
-            uint32_t item = 0;
-            if (me < total) {
-                const uint32_t sw = start[pos];
-                const uint32_t strand = sw >> 31;
-                const uint32_t entry = (sw & 0x7FFFFFFFu) + (me - prefix[pos]);
-                item = entry | (strand << 31);
-                pass = true;
-                if (BL16 && PRE) {
-                    const uint2 words = __ldg(ix.ewords + entry);
-                    pass = seed_precheck<K>(words, s_aux[warp][pos], pair_a, full, ix.two, init_a);
-                }
+            // branch-free: the lanes past the end of the last block run the check on whatever follows the last bucket
+            // (the entry array is padded by 32 entries) and are masked out; entry < 2^31, so adding the offset inside
+            // the bucket never carries into the strand bit
+            const uint32_t item = start[pos] + (me - prefix[pos]);
+            bool pass = me < total;
+            if (BL16 && PRE) {
+                const uint2 words = __ldg(ix.ewords + (item & 0x7FFFFFFFu));
+                pass = seed_precheck<K>(words, s_aux[warp][pos], pair_a, full, ix.two, init_a) && pass;
             }
             const unsigned pm = __ballot_sync(FULL, pass);
             if (pass) queue[qn + __popc(pm & lt_mask)] = item;
