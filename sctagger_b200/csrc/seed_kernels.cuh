@@ -203,8 +203,8 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
     constexpr int NSLOT = 2 * (K + 1) * 32;
     // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
     __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
-    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket | strand << 31
-    __shared__ uint32_t s_aux[SEED_WARPS][PRE ? NSLOT : 1];    // pre-check operands of the slot (see seed_precheck)
+    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket
+    __shared__ uint32_t s_aux[SEED_WARPS][NSLOT];              // strand << 8 | pre-check operands of the slot (see seed_precheck)
     __shared__ uint32_t s_queue[SEED_WARPS][SEED_QUEUE_CAP];   // pre-check survivors: entry | strand << 31
     __shared__ __align__(128) uint2 s_pair[SEED_WARPS][2][16]; // per strand: entry c0 | c1 << 2 = {Eq[c0], Eq[c1]}
     __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
@@ -289,12 +289,14 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
                 if (len) {
                     const int slot = n_slots + __popc(live & lt_mask);
                     prefix[slot] = total + incl - len;
-                    start[slot] = st | ((uint32_t)s << 31);
+                    start[slot] = st;
+                    uint32_t aux = (uint32_t)s << 8;
                     if (PRE) {
                         const uint32_t pre = ix.pre[q], left = (pre >> 5) & 1u;
                         const uint32_t b0 = left ? (uint32_t)(n - lane) : (uint32_t)lane + ((pre >> 9) & 31u);
-                        s_aux[warp][slot] = (2u * (pre & 31u)) | (left << 6) | ((((uint32_t)s) ^ left) << 7) | (b0 << 21);
+                        aux |= (2u * (pre & 31u)) | (left << 6) | ((((uint32_t)s) ^ left) << 7) | (b0 << 21);
                     }
+                    s_aux[warp][slot] = aux;
                 }
                 n_slots += __popc(live);
                 total += __shfl_sync(FULL, incl, 31);
@@ -341,13 +343,14 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
             cur += __popc(heads);
             const uint32_t me = t0 + lane;
             // branch-free: the lanes past the end of the last block run the check on whatever follows the last bucket
-            // (the entry array is padded by 32 entries) and are masked out; entry < 2^31, so adding the offset inside
-            // the bucket never carries into the strand bit
-            const uint32_t item = start[pos] + (me - prefix[pos]);
+            // (the entry array is padded by 32 entries) and are masked out
+            const uint32_t entry = start[pos] + (me - prefix[pos]);
+            const uint32_t aux = s_aux[warp][pos];
+            const uint32_t item = entry | ((aux & 256u) << 23);           // strand in bit 31
             bool pass = me < total;
             if (BL16 && PRE) {
-                const uint2 words = __ldg(ix.ewords + (item & 0x7FFFFFFFu));
-                pass = seed_precheck<K>(words, s_aux[warp][pos], pair_a, full, ix.two, init_a) && pass;
+                const uint2 words = __ldg(ix.ewords + entry);
+                pass = seed_precheck<K>(words, aux, pair_a, full, ix.two, init_a) && pass;
             }
             const unsigned pm = __ballot_sync(FULL, pass);
             if (pass) queue[qn + __popc(pm & lt_mask)] = item;
