@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
     constexpr int NSLOT = 2 * (K + 1) * 32;
     // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
     __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
-    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket
+    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket - index of its first candidate
     __shared__ uint32_t s_aux[SEED_WARPS][NSLOT];              // strand << 8 | pre-check operands of the slot (see seed_precheck)
     __shared__ uint32_t s_queue[SEED_WARPS][SEED_QUEUE_CAP];   // pre-check survivors: entry | strand << 31
     __shared__ __align__(128) uint2 s_pair[SEED_WARPS][2][16]; // per strand: entry c0 | c1 << 2 = {Eq[c0], Eq[c1]}
@@ -288,8 +288,9 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
                 const unsigned live = __ballot_sync(FULL, len != 0u);
                 if (len) {
                     const int slot = n_slots + __popc(live & lt_mask);
-                    prefix[slot] = total + incl - len;
-                    start[slot] = st;
+                    const uint32_t first = total + incl - len;
+                    prefix[slot] = first;
+                    start[slot] = st - first;                        // entry of candidate t = start[slot] + t
                     uint32_t aux = (uint32_t)s << 8;
                     if (PRE) {
                         const uint32_t pre = ix.pre[q], left = (pre >> 5) & 1u;
@@ -344,7 +345,7 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
             const uint32_t me = t0 + lane;
             // branch-free: the lanes past the end of the last block run the check on whatever follows the last bucket
             // (the entry array is padded by 32 entries) and are masked out
-            const uint32_t entry = start[pos] + (me - prefix[pos]);
+            const uint32_t entry = start[pos] + me;
             const uint32_t aux = s_aux[warp][pos];
             const uint32_t item = entry | ((aux & 256u) << 23);           // strand in bit 31
             bool pass = me < total;
@@ -355,8 +356,8 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
             const unsigned pm = __ballot_sync(FULL, pass);
             if (pass) queue[qn + __popc(pm & lt_mask)] = item;
             qn += __popc(pm);
-            __syncwarp();
             if (qn >= 32) {
+                __syncwarp();
                 verify(queue[lane], true);
                 const uint32_t rest = (32 + lane < qn) ? queue[32 + lane] : 0u;
                 __syncwarp();
@@ -365,6 +366,7 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
                 __syncwarp();
             }
         }
+        __syncwarp();
         if (qn > 0) verify(lane < qn ? queue[lane] : 0u, lane < qn);
         __syncwarp();
         if (count <= SEED_LIST_CAP) count = sort_unique(list, tmp, count, lane);
