@@ -206,6 +206,10 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
     __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket - index of its first candidate
     __shared__ uint32_t s_aux[SEED_WARPS][NSLOT];              // strand << 8 | pre-check operands of the slot (see seed_precheck)
     __shared__ uint32_t s_queue[SEED_WARPS][SEED_QUEUE_CAP];   // pre-check survivors: entry | strand << 31
+    // bit t-1 = "a slot starts at candidate t": word j is the slot-start mask of candidates 32j+1 .. 32j+32.  Used when
+    // the segment's candidates fit (always at -mr <= 2 on real data); otherwise the mask is derived from s_prefix.
+    constexpr int MAPW = (K <= 2) ? 128 : 0;
+    __shared__ uint32_t s_map[SEED_WARPS][MAPW > 0 ? MAPW : 1];
     __shared__ __align__(128) uint2 s_pair[SEED_WARPS][2][16]; // per strand: entry c0 | c1 << 2 = {Eq[c0], Eq[c1]}
     __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
     __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
@@ -304,7 +308,17 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
             }
         }
         prefix[n_slots + lane] = 0xFFFFFFFFu;
+        const bool use_map = MAPW > 0 && total <= 32u * MAPW;
+        if (use_map)
+            for (uint32_t w = lane; w < (total + 31u) / 32u; w += 32) s_map[warp][w] = 0u;
         __syncwarp();
+        if (use_map) {
+            for (int i = 1 + lane; i < n_slots; i += 32) {
+                const uint32_t t = prefix[i] - 1u;
+                atomicOr(&s_map[warp][t >> 5], 1u << (t & 31u));
+            }
+            __syncwarp();
+        }
         n_cand += total;
         const uint32_t full = (n >= 31) ? 0xFFFFFFFFu : ((1u << (n + 1)) - 1u);
         int best = K + 1, count = 0;
@@ -338,8 +352,13 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
         int cur = 0;                                                    // slot holding candidate t0 (warp-uniform)
         for (uint32_t t0 = 0; t0 < total; t0 += 32) {
             // slots starting at t0 + r, 1 <= r <= 32, as bit r-1: a lane's slot is cur + #starts at or before it
-            const uint32_t rel = prefix[cur + 1 + lane] - t0 - 1u;
-            const uint32_t heads = __reduce_or_sync(FULL, rel < 32u ? (1u << rel) : 0u);
+            uint32_t heads;
+            if (use_map) {
+                heads = s_map[warp][t0 >> 5];
+            } else {
+                const uint32_t rel = prefix[cur + 1 + lane] - t0 - 1u;
+                heads = __reduce_or_sync(FULL, rel < 32u ? (1u << rel) : 0u);
+            }
             const int pos = cur + __popc(heads & lt_mask);
             cur += __popc(heads);
             const uint32_t me = t0 + lane;
