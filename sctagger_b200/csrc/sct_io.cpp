@@ -76,7 +76,18 @@ int read_whole_file(const char *path, bool gz, std::vector<uint8_t> &out) {
         first = false;
         if ((size_t)got < step) break;
     }
-    gzclose(g);
+    // A truncated stream makes gzread return the bytes inflated so far and only records Z_BUF_ERROR ("unexpected end of
+    // file"); a corrupt tail shows as Z_DATA_ERROR here or as a CRC/length failure in gzclose.  Python's gzip.open
+    // raises EOFError / BadGzipFile for these (the reference's readers, scTagger.py:605, 634), so they are SCT_E_IO.
+    int en = Z_OK;
+    const char *msg = gzerror(g, &en);
+    if (en != Z_OK && en != Z_STREAM_END) {
+        std::string m = (msg && *msg) ? msg : "unexpected end of file";
+        gzclose(g);
+        return fail(SCT_E_IO, "gzip error on %s: %s", path, m.c_str());
+    }
+    const int crc = gzclose(g);
+    if (crc != Z_OK) return fail(SCT_E_IO, "gzip error on %s: %s", path, crc == Z_BUF_ERROR ? "unexpected end of file" : "corrupt stream");
     return SCT_OK;
 }
 

@@ -110,6 +110,8 @@ int reset_counts(sct_wl_handle *h) {
     if (h->n_words > 0) {
         CUDA_TRY(cudaMemset(h->d_counts, 0, (size_t)h->n_words * sizeof(unsigned int)));
         CUDA_TRY(cudaMemset(h->d_first, 0xFF, (size_t)h->n_words * sizeof(unsigned long long)));
+        // the memsets run on the legacy stream, the count kernels on non-blocking streams that do not order behind it
+        CUDA_TRY(cudaDeviceSynchronize());
     }
     h->next_rid = 0;
     return SCT_OK;

@@ -212,3 +212,33 @@ def test_indexed_gzip_members_parallel_and_mixed_files(tmp_path):
         assert len(got) == n + extra
         segs = _unpack(got.seg_bytes, got.offsets)
         assert segs.count(b"ACGTACGTACGTACGTACGTAC") == n and (extra == 0 or b"GGGG" in segs)
+
+
+@pytest.mark.parametrize("cut", [1, 9, 30, "half"])
+def test_truncated_or_corrupt_gzip_is_an_os_error(tmp_path, cut):
+    """gzip.open raises EOFError / BadGzipFile on a truncated or corrupt stream (the reference's readers,
+    scTagger.py:605, 634); the native reader must not hand back the rows inflated so far."""
+    rows = b"".join(b"r%d\t0\t0\tACGTACGTACGTACGTACGTAC\n" % i for i in range(20000))
+    whole = gzip.compress(rows)
+    data = whole[: len(whole) // 2] if cut == "half" else whole[:-cut]
+    p = tmp_path / "trunc.tsv.gz"
+    p.write_bytes(data)
+    with pytest.raises(EOFError):
+        gzip.open(p, "rb").read()
+    with pytest.raises(OSError):
+        mt.read_long_reads(str(p), 4)
+    # the native writer's multi-member files: a truncated last member must fail as well, not fall back silently
+    names = [b"r%d" % i for i in range(40000)]
+    nb, no = hm.pack(names)
+    rb, ro = hm.pack([b"ACGTACGTACGTACGTACGTAC"] * len(names))
+    z = np.zeros(len(names), np.int64)
+    ours = lr.format_rows(lr.Reads(nb, no, rb, ro), (z, z, z, z), gzip_level=1, threads=4)
+    q = tmp_path / "trunc_members.tsv.gz"
+    q.write_bytes(ours[: len(ours) // 2] if cut == "half" else ours[:-cut])
+    with pytest.raises(OSError):
+        mt.read_long_reads(str(q), 4)
+    bad = bytearray(whole)
+    bad[len(bad) // 2] ^= 0xFF                                            # corrupt deflate data / CRC mismatch
+    p.write_bytes(bytes(bad))
+    with pytest.raises(OSError):
+        mt.read_long_reads(str(p), 4)
