@@ -101,12 +101,15 @@ int sct_stats(sct_handle *h, int64_t stats[8]);
  *   "path"                                0 = automatic (seeded kernel for clean segments of <= 31 bases), 1 = force the
  *                                         generic bit-parallel kernel, 2 = force the DP kernel, 3 = use the all-pairs tile
  *                                         kernel instead of the seeded one
+ *   "stream_segments", "ramp_segments"    segments per streamed chunk of sct_match, and of its first chunk (the size
+ *                                         doubles from chunk to chunk up to stream_segments so the pipeline fills fast)
  *   "seed_ctas_per_sm"                    resident CTAs per SM of the seeded kernel (grid = SMs x this)
  *   "seed_prefilter"                      0 = verify every seeded candidate in full (no anchored pre-check); same results
  */
 int sct_set_option(sct_handle *h, const char *key, int64_t value);
 
-/* Largest batch (segments / bytes) sct_stage accepts with the handle's chunk sizing. */
+/* Chunk sizing derived from mem_gb (segments / bytes per streamed chunk of sct_match).  sct_stage itself accepts any
+ * batch that fits the device. */
 int sct_chunk_capacity(sct_handle *h, int64_t *max_segments, int64_t *max_bytes);
 
 /*
@@ -118,6 +121,29 @@ int sct_measure_int32_peak(int device, int mode, int repeats, double *lane_ops_p
 
 /* Wipe L2 by overwriting a buffer larger than it (used between timed bench iterations). */
 int sct_flush_l2(sct_handle *h);
+
+/*
+ * Page-locked host memory.  The reference keeps lr_segs / lr_segs_idxs in multiprocessing.RawArray's
+ * (scTagger.py:617-626) so that forked workers read them without a copy; the equivalent here is host memory the GPU's
+ * copy engines can read and write directly.  Every array handed to sct_match that lies in page-locked memory —
+ * allocated with sct_host_alloc, pinned in place with sct_host_register, or by any other cudaHostAlloc /
+ * cudaHostRegister — is copied from / to without the staging pass through the library's own pinned buffers: inputs go
+ * caller -> device, results device -> caller, and the host threads touch no segment byte.  Pageable arrays keep
+ * working (they are staged by the handle's host threads).
+ */
+int sct_host_alloc(size_t bytes, void **out);
+int sct_host_free(void *p);
+int sct_host_register(void *p, size_t bytes);
+int sct_host_unregister(void *p);
+
+/* Live work counters of the last sct_match / sct_run_staged (device-side, summed over the chunks): [0] index bucket
+ * probes, [1] full automaton verifications (16 barcode characters each), [2] anchored pre-checks, [3] segments set up by
+ * the seeded kernel, [4..7] reserved.  bench.py derives `roofline.useful` from these. */
+int sct_work_counters(sct_handle *h, int64_t counters[8]);
+
+/* Name of the kernel that scores the clean segments with the handle's parameters and options (the dominant kernel of a
+ * pass; bench.py labels its roofline with it). */
+const char *sct_kernel_name(sct_handle *h);
 
 /* ---------------------------------------------------------------------------------------------------------------------
  * extract_lr_bc adapter alignment (BASELINE config 5).  The reference's seam is

@@ -19,6 +19,7 @@ EXPORTS = (
     "sct_device_count", "sct_last_error", "sct_create", "sct_destroy", "sct_match", "sct_stage",
     "sct_run_staged", "sct_fetch_staged", "sct_stats", "sct_set_option", "sct_chunk_capacity",
     "sct_measure_int32_peak", "sct_flush_l2",
+    "sct_host_alloc", "sct_host_free", "sct_host_register", "sct_host_unregister", "sct_work_counters", "sct_kernel_name",
     "sct_align_create", "sct_align_destroy", "sct_align", "sct_align_stage", "sct_align_run_staged",
     "sct_align_stats", "sct_align_set_option",
     "sct_io_read_long_reads", "sct_io_read_fastqs", "sct_io_reads_info", "sct_io_reads_free",
@@ -82,6 +83,18 @@ def lib():
                                                  ctypes.POINTER(ctypes.c_double)]
             L.sct_flush_l2.restype = ctypes.c_int
             L.sct_flush_l2.argtypes = [_vp]
+            L.sct_host_alloc.restype = ctypes.c_int
+            L.sct_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(_vp)]
+            L.sct_host_free.restype = ctypes.c_int
+            L.sct_host_free.argtypes = [_vp]
+            L.sct_host_register.restype = ctypes.c_int
+            L.sct_host_register.argtypes = [_vp, ctypes.c_size_t]
+            L.sct_host_unregister.restype = ctypes.c_int
+            L.sct_host_unregister.argtypes = [_vp]
+            L.sct_work_counters.restype = ctypes.c_int
+            L.sct_work_counters.argtypes = [_vp, _i64p]
+            L.sct_kernel_name.restype = ctypes.c_char_p
+            L.sct_kernel_name.argtypes = [_vp]
             _i8p = ctypes.POINTER(ctypes.c_int8)
             L.sct_align_create.restype = ctypes.c_int
             L.sct_align_create.argtypes = [ctypes.c_int, _u8p, ctypes.c_int32, ctypes.c_int32, ctypes.c_double,
@@ -169,6 +182,60 @@ def _as_u8(a):
 
 STAT_NAMES = ("launches", "fast_segments", "generic_segments", "h2d_bytes", "d2h_bytes", "chunks",
               "dp_segments", "seed_candidates")
+WORK_NAMES = ("probes", "verifications", "prechecks", "segments_set_up", "reserved4", "reserved5", "reserved6",
+              "reserved7")
+
+
+class Pinned:
+    """One page-locked host allocation (sct_host_alloc) exposed as a numpy array (`.array`).  Arrays living in such
+    memory are copied from / to by the GPU's copy engines directly: sct_match skips its staging pass for them.  The
+    memory is released by close() or when the object is collected — keep the object alive as long as the array is used."""
+
+    def __init__(self, shape, dtype):
+        dtype = np.dtype(dtype)
+        shape = (int(shape),) if np.isscalar(shape) else tuple(int(x) for x in shape)
+        count = int(np.prod(shape)) if shape else 1
+        self.nbytes = max(64, count * dtype.itemsize)
+        self._p = _vp()
+        _check(lib().sct_host_alloc(self.nbytes, ctypes.byref(self._p)))
+        buf = (ctypes.c_uint8 * self.nbytes).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+
+    @classmethod
+    def copy_of(cls, a):
+        a = np.asarray(a)
+        p = cls(a.shape, a.dtype)
+        np.copyto(p.array, a)
+        return p
+
+    def close(self):
+        if getattr(self, "_p", None) is not None and self._p.value:
+            self.array = None
+            lib().sct_host_free(self._p)
+            self._p = _vp()
+
+    __del__ = close
+
+
+class ResultBuffers:
+    """Caller-owned, reusable, page-locked result arrays for Matcher.match(..., out=...): the device writes min_ed, n_ties
+    and tie_offsets straight into them (no staging, no host pass).  Capacity in segments; reuse it across calls — the
+    arrays of one call are overwritten by the next call that uses the same buffers."""
+
+    def __init__(self, capacity: int):
+        self.capacity = int(capacity)
+        self._min = Pinned(max(self.capacity, 1), np.int32)
+        self._nt = Pinned(max(self.capacity, 1), np.int32)
+        self._toff = Pinned(self.capacity + 1, np.int64)
+
+    def views(self, n):
+        if n > self.capacity:
+            raise ValueError(f"ResultBuffers of capacity {self.capacity} cannot hold {n} segments")
+        return self._min.array[:max(n, 1)], self._nt.array[:max(n, 1)], self._toff.array[:n + 1]
+
+    def close(self):
+        for x in (self._min, self._nt, self._toff):
+            x.close()
 
 
 class Matcher:
@@ -217,19 +284,28 @@ class Matcher:
             return np.zeros(0, dtype=np.int32)
         return np.ctypeslib.as_array(ids, shape=(total,)).copy()
 
-    def match(self, seg_bytes: np.ndarray, offsets: np.ndarray):
-        """sct_match: host buffers in, host buffers out (chunked, pinned, double-buffered inside)."""
+    def match(self, seg_bytes: np.ndarray, offsets: np.ndarray, out: "ResultBuffers" = None, copy_ties: bool = True):
+        """sct_match: host buffers in, host buffers out (chunked, double-buffered async copies inside).
+        Arrays in page-locked memory (`Pinned`, `ResultBuffers`) are copied from / to directly; pageable numpy arrays
+        are staged by the library's host threads.  With `out`, the result arrays are views of the caller's
+        ResultBuffers; with copy_ties=False, tie_ids is a view of the library-owned buffer, valid until the next call
+        on this Matcher (the C ABI's own contract)."""
         from .match_trie import MatchResult
         sb = _as_u8(seg_bytes)
         off = np.ascontiguousarray(offsets, dtype=np.int64)
         n = off.shape[0] - 1
-        min_ed, n_ties, tie_off = self._out(n)
+        min_ed, n_ties, tie_off = self._out(n) if out is None else out.views(n)
         ids = _i32p()
         total = ctypes.c_int64(0)
         _check(lib().sct_match(self._h, _ptr(sb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), n,
                                _ptr(min_ed, ctypes.c_int32), _ptr(n_ties, ctypes.c_int32),
                                _ptr(tie_off, ctypes.c_int64), ctypes.byref(ids), ctypes.byref(total)))
-        return MatchResult(min_ed[:n], n_ties[:n], tie_off, self._ties(ids, int(total.value)))
+        t = int(total.value)
+        if copy_ties or t == 0:
+            ties = self._ties(ids, t)
+        else:
+            ties = np.ctypeslib.as_array(ids, shape=(t,))
+        return MatchResult(min_ed[:n], n_ties[:n], tie_off, ties)
 
     def stage(self, seg_bytes: np.ndarray, offsets: np.ndarray):
         sb = _as_u8(seg_bytes)
@@ -257,6 +333,14 @@ class Matcher:
         s = np.zeros(8, dtype=np.int64)
         _check(lib().sct_stats(self._h, _ptr(s, ctypes.c_int64)))
         return dict(zip(STAT_NAMES, s.tolist()))
+
+    def kernel_name(self) -> str:
+        return lib().sct_kernel_name(self._h).decode()
+
+    def work_counters(self) -> dict:
+        s = np.zeros(8, dtype=np.int64)
+        _check(lib().sct_work_counters(self._h, _ptr(s, ctypes.c_int64)))
+        return dict(zip(WORK_NAMES, s.tolist()))
 
     def chunk_capacity(self):
         a, b = ctypes.c_int64(0), ctypes.c_int64(0)

@@ -7,5 +7,5 @@ NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 HOSTCXX="${SCT_HOSTCXX:-/usr/bin/g++}"
 "$NVCC" -ccbin "$HOSTCXX" -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
     -Xptxas -v -shared -Xcompiler -fPIC,-O3,-Wall,-pthread \
-    -o "$OUT" "$HERE/sctagger_b200.cu" "$HERE/sct_align.cu" "$HERE/sct_wl.cu" "$HERE/sct_io.cpp" -lz "$@"
+    -o "$OUT" "$HERE/sctagger_b200.cu" "$HERE/sct_align.cu" "$HERE/sct_wl.cu" "$HERE/sct_io.cpp" -lz -ldl "$@"
 echo "built $OUT"

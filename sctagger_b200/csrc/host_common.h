@@ -2,6 +2,7 @@
 // (passive waiting), parallel memcpy and small RAII-less free helpers.  Internal — not part of the C ABI.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: a no-op unless a profiler injects itself (nsys / ncu --nvtx)
 #include "../../include/sctagger_b200.h"
 
 #include <algorithm>
@@ -32,6 +33,14 @@ struct Trace {
     }
 };
 inline thread_local Trace g_tr;
+
+// NVTX range around a host phase (stage / H2D + kernels / wait + D2H / format): SURVEY.md §5 "tracing".
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange &) = delete;
+    NvtxRange &operator=(const NvtxRange &) = delete;
+};
 
 inline int fail(int code, const char *fmt, ...) {
     char buf[1024];

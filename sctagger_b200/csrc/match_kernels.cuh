@@ -41,6 +41,11 @@ struct Counters {                    // device-side cursors, zeroed before every
     unsigned int cur_fast, cur_gen, cur_ovf, cur_dp;
     unsigned long long tie_cursor;   // bump allocator over tie_buf (may run past tie_cap: the pass is then redone)
     unsigned long long n_cand;       // seeded kernel: candidates generated (statistics)
+    unsigned int n_bad;              // segments whose offsets are decreasing or leave the chunk (the call fails)
+    unsigned int pad_;
+    // live work counters of the seeded kernels (bench.py's roofline.useful): bucket probes, full verifications,
+    // pre-checks, segments set up
+    unsigned long long n_probe, n_verify, n_precheck, n_setup;
 };
 
 struct MatchParams {
@@ -49,7 +54,8 @@ struct MatchParams {
     int n_barcodes;
     int bl;                          // barcode length (<= 16 for the bit-parallel kernels)
     const uint8_t *seg_bytes;        // raw segment bytes of the chunk
-    const long long *seg_off;        // n+1 offsets into seg_bytes
+    const long long *seg_off;        // n+1 offsets in the CALLER's numbering: byte j of the chunk is offset b0 + j
+    long long b0;
     const uint8_t *rec;              // REC_BYTES per segment (fast segments only)
     const uint8_t *colinfo;          // per raw byte: (2*code) | v-bits << 3 (generic segments only)
     const uint8_t *segflag;
@@ -405,8 +411,8 @@ __global__ void __launch_bounds__(GEN_THREADS) match_generic_kernel(const MatchP
         idx = __shfl_sync(FULL, idx, 0);
         if (idx >= n_items) break;
         const int seg = items[idx];
-        const long long o = p.seg_off[seg];
-        const int n = (int)(p.seg_off[seg + 1] - o);
+        const long long o = p.seg_off[seg] - p.b0;
+        const int n = (int)(p.seg_off[seg + 1] - p.b0 - o);
         const uint8_t flag = p.segflag[seg];
         const bool is_fast = (flag & SEG_FAST) != 0;
         const uint8_t *cols = is_fast ? p.rec + (size_t)seg * REC_BYTES : p.colinfo + o;
@@ -435,6 +441,7 @@ __device__ __forceinline__ int base_code(uint8_t b) {   // -1 for anything but u
 }
 
 __global__ void __launch_bounds__(256) prep_kernel(const uint8_t *__restrict__ bytes, const long long *__restrict__ off,
+                                                   long long b0, long long nbytes,
                                                    int n_seg, int bl, int K, int kpre, int path /*0 auto,1 generic,2 dp*/,
                                                    int fast_max /* longest segment of the fast path */,
                                                    unsigned long long *__restrict__ pk /* 2-bit packed text, or NULL */,
@@ -445,8 +452,12 @@ __global__ void __launch_bounds__(256) prep_kernel(const uint8_t *__restrict__ b
                                                    int *__restrict__ n_ties) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_seg) return;
-    const long long o = off[i];
-    const long long L = off[i + 1] - o;
+    const long long o = off[i] - b0;
+    long long L = off[i + 1] - b0 - o;
+    if (L < 0 || o < 0 || o + L > nbytes) {   // the caller's offsets are not non-decreasing inside the chunk: the call fails
+        atomicAdd(&ctr->n_bad, 1u);
+        L = 0;
+    }
     if (L < bl - K) {   // cannot hold a barcode within K edits: the reference emits no row (scTagger.py:681)
         segflag[i] = SEG_SHORT;
         min_ed[i] = -1;
@@ -573,8 +584,8 @@ __global__ void __launch_bounds__(128) match_dp_kernel(const MatchParams p, cons
         idx = __shfl_sync(FULL, idx, 0);
         if (idx >= n_items) break;
         const int seg = dp_list[idx];
-        const long long o = p.seg_off[seg];
-        const int n = (int)(p.seg_off[seg + 1] - o);
+        const long long o = p.seg_off[seg] - p.b0;
+        const int n = (int)(p.seg_off[seg + 1] - p.b0 - o);
         const uint8_t *s = p.seg_bytes + o;
         // pass 1: minimum
         int best = q.K + 1;
@@ -653,7 +664,11 @@ __global__ void __launch_bounds__(SCAN_BLOCK) scan_block_sums(const int *__restr
     }
 }
 
-__global__ void __launch_bounds__(1024) scan_block_prefix(long long *__restrict__ block_sums, int n_blocks, long long *__restrict__ total) {
+// total[0] = ties of this chunk; total[1] = ties of all earlier chunks of the call (`run` is the device-side running sum,
+// advanced once per chunk — not again when the pass is repeated after the tie buffer grew), so that tie_offsets leave
+// the device already in the call's numbering and the host never touches them.
+__global__ void __launch_bounds__(1024) scan_block_prefix(long long *__restrict__ block_sums, int n_blocks, long long *__restrict__ total,
+                                                          long long *__restrict__ run, int redo) {
     // single block: serial over chunks of 1024 block sums, exclusive prefix in place
     __shared__ long long sh[1024];
     __shared__ long long carry;
@@ -677,13 +692,20 @@ __global__ void __launch_bounds__(1024) scan_block_prefix(long long *__restrict_
         if (threadIdx.x == 1023) carry = c + incl;
         __syncthreads();
     }
-    if (threadIdx.x == 0) *total = carry;
+    if (threadIdx.x == 0) {
+        total[0] = carry;
+        if (!redo) {
+            const long long b = *run;
+            total[1] = b;
+            *run = b + carry;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(SCAN_BLOCK) scan_gather(const int *__restrict__ n_ties, int n, const long long *__restrict__ block_prefix,
                                                           const unsigned int *__restrict__ tie_start, const int *__restrict__ tie_buf,
                                                           long long *__restrict__ tie_off, int *__restrict__ tie_out,
-                                                          unsigned long long tie_cap) {
+                                                          unsigned long long tie_cap, const long long *__restrict__ total) {
     __shared__ long long warp_sums[32];
     const int i = blockIdx.x * SCAN_BLOCK + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -709,8 +731,9 @@ __global__ void __launch_bounds__(SCAN_BLOCK) scan_gather(const int *__restrict_
     __syncthreads();
     const long long excl = block_prefix[blockIdx.x] + warp_sums[warp] + incl - c;
     if (i < n) {
-        tie_off[i] = excl;
-        if (i == n - 1) tie_off[n] = excl + c;
+        const long long base = total[1];       // tie_out stays chunk-local, tie_off is in the call's numbering
+        tie_off[i] = base + excl;
+        if (i == n - 1) tie_off[n] = base + excl + c;
         // when the bump allocator ran past tie_cap the host grows the buffers and redoes the pass: write nothing here
         if (c > 0 && (unsigned long long)(excl + c) <= tie_cap) {
             const unsigned int s = tie_start[i];

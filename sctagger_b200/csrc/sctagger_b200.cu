@@ -14,6 +14,12 @@ using namespace scth;
 
 namespace {
 
+// Chunks in flight per handle.  Three, not two: the small trailing kernels of chunk c (generic, scan: blocks of up to
+// 1024 threads) cannot be placed while the persistent match kernel of chunk c+1 fills the SMs, so they run when that
+// kernel ends — with two slots the host would sit in "wait for chunk c" until then and enqueue chunk c+2 too late; with
+// three it has already queued chunk c+2 and the GPU goes from one match kernel straight into the next.
+constexpr int N_SLOTS = 3;
+
 struct Slot {
     int64_t cap_segs = 0, cap_bytes = 0;
     unsigned long long tie_cap = 0;
@@ -22,9 +28,8 @@ struct Slot {
     long long *h_off = nullptr;
     int *h_min = nullptr, *h_nt = nullptr;
     long long *h_toff = nullptr;
-    int *h_ties = nullptr;
     Counters *h_ctr = nullptr;
-    long long *h_total = nullptr;
+    long long *h_total = nullptr;      // [0] ties of the chunk, [1] ties of all chunks before it (device-side running sum)
     // device
     uint8_t *d_bytes = nullptr, *d_colinfo = nullptr, *d_rec = nullptr, *d_segflag = nullptr;
     long long *d_off = nullptr;
@@ -34,13 +39,18 @@ struct Slot {
     int *d_min = nullptr, *d_nt = nullptr;
     unsigned int *d_tstart = nullptr;
     int *d_tiebuf = nullptr, *d_tieout = nullptr;
-    long long *d_toff = nullptr, *d_bsums = nullptr, *d_total = nullptr;
+    long long *d_toff = nullptr, *d_bsums = nullptr, *d_total = nullptr;   // d_total: [0] chunk total, [1] chunk base
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_start = nullptr, ev_k0 = nullptr, ev_k1 = nullptr, ev_end = nullptr;
     // in flight
     int64_t n = 0, nbytes = 0, first = 0;
+    long long b0 = 0;               // offset of the chunk's first byte in the caller's numbering (seg_offsets stay absolute)
     bool busy = false;
     bool copies_enqueued = false;   // the fixed-size result copies follow the pass on the stream (sct_match)
+    bool redo = false;              // pass repeated after the tie buffer grew: the running tie base is not advanced again
+    // where the fixed-size results of the chunk go: the caller's arrays when they are pinned, else the slot's staging
+    int *dst_min = nullptr, *dst_nt = nullptr;
+    long long *dst_toff = nullptr;
 };
 
 }  // namespace
@@ -62,6 +72,7 @@ struct sct_handle {
     size_t fast_smem = 0;
     int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
     int64_t stream_segs = 0;                    // segments per streamed chunk of sct_match (<= chunk_segs)
+    int64_t ramp_segs = 1 << 15;                // size of the first streamed chunk (doubles up to stream_segs)
     int host_threads = 1;        // worker threads for staging / un-staging (from -t, capped)
     HostPool *pool = nullptr;
     int tie_per_seg = 8;
@@ -71,9 +82,15 @@ struct sct_handle {
     int ovf_blocks = 16, ovf_cap = 0;
     uint8_t *d_flush = nullptr;
     size_t flush_bytes = 256u << 20;
-    Slot slot[2];
-    std::vector<int32_t> ties_host;
+    Slot slot[N_SLOTS];
+    int32_t *ties_pinned = nullptr;             // tie ids of the whole call (library-owned, pinned; sct_match's *tie_ids)
+    int64_t ties_cap = 0;
+    long long *d_tie_run = nullptr;             // device-side running sum of ties over the chunks of one call
+    // which of the caller's arrays are page-locked (cudaHostAlloc / cudaHostRegister / sct_host_alloc): those are
+    // copied from / to directly, without the staging pass through the slot's pinned buffers
+    bool in_bytes_pinned = false, in_off_pinned = false, out_min_pinned = false, out_nt_pinned = false, out_toff_pinned = false;
     int64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int64_t work[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // live work counters of the seeded kernels (sct_work_counters)
     bool staged = false, staged_ran = false;
 };
 
@@ -81,7 +98,7 @@ namespace {
 
 int free_slot(Slot &s) {
     host_free(s.h_bytes); host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
-    host_free(s.h_ties); host_free(s.h_ctr); host_free(s.h_total);
+    host_free(s.h_ctr); host_free(s.h_total);
     dev_free(s.d_bytes); dev_free(s.d_colinfo); dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off);
     dev_free(s.d_fast); dev_free(s.d_gen); dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_ctr);
     dev_free(s.d_pk);
@@ -95,11 +112,9 @@ int free_slot(Slot &s) {
 int alloc_ties(Slot &s, unsigned long long cap) {
     dev_free(s.d_tiebuf);
     dev_free(s.d_tieout);
-    host_free(s.h_ties);
     s.tie_cap = 0;
     CUDA_TRY(cudaMalloc(&s.d_tiebuf, cap * sizeof(int)));
     CUDA_TRY(cudaMalloc(&s.d_tieout, cap * sizeof(int)));
-    CUDA_TRY(cudaMallocHost(&s.h_ties, cap * sizeof(int)));
     s.tie_cap = cap;
     return SCT_OK;
 }
@@ -112,9 +127,13 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         CUDA_TRY(cudaEventCreate(&s.ev_k1));
         CUDA_TRY(cudaEventCreate(&s.ev_end));
         CUDA_TRY(cudaMallocHost(&s.h_ctr, sizeof(Counters)));
-        CUDA_TRY(cudaMallocHost(&s.h_total, sizeof(long long)));
+        CUDA_TRY(cudaMallocHost(&s.h_total, 2 * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_ctr, sizeof(Counters)));
-        CUDA_TRY(cudaMalloc(&s.d_total, sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_total, 2 * sizeof(long long)));
+        if (!h->d_tie_run) {
+            CUDA_TRY(cudaMalloc(&h->d_tie_run, sizeof(long long)));
+            CUDA_TRY(cudaMemset(h->d_tie_run, 0, sizeof(long long)));
+        }
     }
     if (segs > s.cap_segs) {
         const int64_t c = std::max<int64_t>(segs, 1024);
@@ -167,6 +186,7 @@ MatchParams make_params(sct_handle *h, Slot &s) {
     p.bl = h->bl;
     p.seg_bytes = s.d_bytes;
     p.seg_off = s.d_off;
+    p.b0 = s.b0;
     p.rec = s.d_rec;
     p.colinfo = s.d_colinfo;
     p.segflag = s.d_segflag;
@@ -186,7 +206,8 @@ MatchParams make_params(sct_handle *h, Slot &s) {
 }
 
 template <int K>
-int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 none, 1 tile kernel, 2 seeded kernel */) {
+int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 none, 1 tile kernel, 2 seeded kernel */,
+                 cudaEvent_t after /* everything behind the main kernel waits for this event (may be null) */) {
     if (fast == 2) {
         // seeded kernel: small static shared memory, many resident warps (latency-bound gathers + verification)
         const int grid = h->sm_count * h->seed_ctas_per_sm;
@@ -206,6 +227,9 @@ int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 non
         CUDA_TRY(cudaGetLastError());
         CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
     }
+    // the generic kernels share the handle's overflow scratch with the other slot's chunk, the finalize advances the
+    // running tie base: both stay behind that chunk's finalize
+    if (after && fast) CUDA_TRY(cudaStreamWaitEvent(s.stream, after, 0));
     match_generic_kernel<K><<<h->sm_count * 4, GEN_THREADS, 0, s.stream>>>(p, 0);
     CUDA_TRY(cudaGetLastError());
     match_generic_kernel<K><<<h->ovf_blocks, GEN_THREADS, 0, s.stream>>>(p, 1);
@@ -221,15 +245,22 @@ int fast_kind(const sct_handle *h) {
 }
 
 // Enqueue one full pass over the n segments resident in slot s (no host synchronisation).
-int enqueue_pass(sct_handle *h, Slot &s, int64_t n) {
+int enqueue_pass(sct_handle *h, Slot &s, int64_t n, Slot *prev = nullptr) {
     const int fk = fast_kind(h);
+    // Ordering against the chunk in the other slot (sct_match): this chunk's kernels start behind that chunk's MATCH
+    // kernel (ev_k1), so its small trailing kernels (generic, scan) overlap this chunk's prep + match kernel instead of
+    // leaving the GPU to themselves; only the finalize, which advances the running tie base, waits for that chunk's
+    // finalize (ev_end).  Without any ordering the two streams run both chunks' persistent kernels side by side, they
+    // finish together, and the GPU idles while the host handles one chunk and prepares the next.
+    const bool chained = prev && prev->busy;
+    if (chained) CUDA_TRY(cudaStreamWaitEvent(s.stream, fk ? prev->ev_k1 : prev->ev_end, 0));
     const int path = h->use_dp || h->path_override == 2 ? 2 : (fk ? 0 : 1);
     MatchParams p = make_params(h, s);
     CUDA_TRY(cudaEventRecord(s.ev_start, s.stream));
     CUDA_TRY(cudaMemsetAsync(s.d_ctr, 0, sizeof(Counters), s.stream));
     int launches = 0;
     if (n > 0) {
-        prep_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.d_bytes, s.d_off, (int)n, h->bl, h->K, h->kpre, path,
+        prep_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.d_bytes, s.d_off, s.b0, s.nbytes, (int)n, h->bl, h->K, h->kpre, path,
                                                                      fk == 2 ? SEED_MAX_LEN : FAST_MAX_LEN,
                                                                      fk == 2 ? s.d_pk : nullptr, s.d_rec, s.d_colinfo, s.d_segflag, s.d_fast, s.d_gen,
                                                                      s.d_dp, s.d_ctr, s.d_min, s.d_nt);
@@ -250,41 +281,43 @@ int enqueue_pass(sct_handle *h, Slot &s, int64_t n) {
             ++launches;
         } else {
             switch (h->K) {
-                case 0: TRY(launch_match<0>(h, s, p, fk)); break;
-                case 1: TRY(launch_match<1>(h, s, p, fk)); break;
-                case 2: TRY(launch_match<2>(h, s, p, fk)); break;
-                default: TRY(launch_match<3>(h, s, p, fk)); break;
+                case 0: TRY(launch_match<0>(h, s, p, fk, chained ? prev->ev_end : nullptr)); break;
+                case 1: TRY(launch_match<1>(h, s, p, fk, chained ? prev->ev_end : nullptr)); break;
+                case 2: TRY(launch_match<2>(h, s, p, fk, chained ? prev->ev_end : nullptr)); break;
+                default: TRY(launch_match<3>(h, s, p, fk, chained ? prev->ev_end : nullptr)); break;
             }
             if (!fk) CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
             launches += fk ? 3 : 2;
         }
+        if (chained) CUDA_TRY(cudaStreamWaitEvent(s.stream, prev->ev_end, 0));
         const int nb = (int)((n + SCAN_BLOCK - 1) / SCAN_BLOCK);
         scan_block_sums<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums);
         CUDA_TRY(cudaGetLastError());
-        scan_block_prefix<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total);
+        scan_block_prefix<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total, h->d_tie_run, s.redo ? 1 : 0);
         CUDA_TRY(cudaGetLastError());
-        scan_gather<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums, s.d_tstart, s.d_tiebuf, s.d_toff, s.d_tieout, s.tie_cap);
+        scan_gather<<<nb, SCAN_BLOCK, 0, s.stream>>>(s.d_nt, (int)n, s.d_bsums, s.d_tstart, s.d_tiebuf, s.d_toff, s.d_tieout, s.tie_cap, s.d_total);
         CUDA_TRY(cudaGetLastError());
         launches += 3;
     } else {
         CUDA_TRY(cudaEventRecord(s.ev_k0, s.stream));
         CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
-        CUDA_TRY(cudaMemsetAsync(s.d_total, 0, sizeof(long long), s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.d_total, 0, 2 * sizeof(long long), s.stream));
     }
     CUDA_TRY(cudaEventRecord(s.ev_end, s.stream));
     CUDA_TRY(cudaMemcpyAsync(s.h_ctr, s.d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.h_total, s.d_total, sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_total, s.d_total, 2 * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
     h->stats[0] += launches;
     return SCT_OK;
 }
 
-// Fixed-size results (min_ed, n_ties, tie offsets) start their way back right behind the kernels of the pass.
+// Fixed-size results (min_ed, n_ties, tie offsets) start their way back right behind the kernels of the pass, straight
+// into the caller's arrays when those are page-locked.
 int enqueue_result_copies(Slot &s) {
     const int64_t n = s.n;
     if (n <= 0) return SCT_OK;
-    CUDA_TRY(cudaMemcpyAsync(s.h_min, s.d_min, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.h_nt, s.d_nt, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.h_toff, s.d_toff, (size_t)(n + 1) * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.dst_min, s.d_min, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.dst_nt, s.d_nt, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.dst_toff, s.d_toff, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
     return SCT_OK;
 }
 
@@ -294,91 +327,123 @@ int complete_pass(sct_handle *h, Slot &s) {
         const double t0 = Trace::now();
         CUDA_TRY(cudaStreamSynchronize(s.stream));
         g_tr.t_wait += Trace::now() - t0;
+        if (s.h_ctr->n_bad)
+            return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld: %u bad segments)",
+                        (long long)s.first, s.h_ctr->n_bad);
+        if (s.h_ctr->tie_cursor > 0xFFFFFFFFull)
+            return fail(SCT_E_UNSUPPORTED, "more than 2^32 ties in one chunk of %lld segments: lower -m", (long long)s.n);
         if (s.h_ctr->tie_cursor <= s.tie_cap) {
             h->stats[1] += s.h_ctr->n_fast;
             h->stats[2] += s.h_ctr->n_gen + s.h_ctr->n_ovf;
             h->stats[6] += s.h_ctr->n_dp;
             h->stats[7] += (int64_t)s.h_ctr->n_cand;
+            h->work[0] += (int64_t)s.h_ctr->n_probe;
+            h->work[1] += (int64_t)s.h_ctr->n_verify;
+            h->work[2] += (int64_t)s.h_ctr->n_precheck;
+            h->work[3] += (int64_t)s.h_ctr->n_setup;
+            s.redo = false;
             return SCT_OK;
         }
         const unsigned long long need = s.h_ctr->tie_cursor + 4096;
         TRY(alloc_ties(s, need));
+        s.redo = true;
         TRY(enqueue_pass(h, s, s.n));
         if (s.copies_enqueued) TRY(enqueue_result_copies(s));
     }
+    s.redo = false;
     return fail(SCT_E_STATE, "tie buffer did not converge");
 }
 
-// Copy chunk [first, first+n) of the caller's arrays into the slot's pinned staging and start H2D + pass.
-// `prev` = the slot holding the chunk before this one (still in flight): this chunk's kernels are ordered behind that
-// chunk's kernels with an event.  Without it the two streams run both chunks' persistent kernels side by side, they
-// finish together, and the GPU then idles while the host un-stages one chunk and stages the next — measured: the host
-// time (47 ms per 10 M segments) added to the kernel time instead of hiding behind it.  The H2D copy of this chunk
-// (issued before the wait) and the D2H copies of the previous one still overlap the kernels.
-int start_chunk(sct_handle *h, Slot &s, Slot *prev, const uint8_t *seg_bytes, const int64_t *off, int64_t first, int64_t n) {
+// Is [p, p + bytes) page-locked host memory the copy engines can read / write directly?
+bool is_pinned(const void *p, size_t bytes) {
+    if (!p || bytes == 0) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    if (a.type != cudaMemoryTypeHost) return false;
+    if (cudaPointerGetAttributes(&a, (const char *)p + bytes - 1) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// The library-owned pinned buffer holding the tie ids of the whole call grows geometrically and keeps its content.
+int ensure_ties(sct_handle *h, int64_t need, int64_t keep) {
+    if (need <= h->ties_cap) return SCT_OK;
+    const int64_t cap = std::max<int64_t>({need, 2 * h->ties_cap, (int64_t)1 << 16});
+    int32_t *fresh = nullptr;
+    CUDA_TRY(cudaMallocHost(&fresh, (size_t)cap * sizeof(int32_t)));
+    if (keep > 0) par_memcpy(h->pool, fresh, h->ties_pinned, (size_t)keep * sizeof(int32_t));
+    host_free(h->ties_pinned);
+    h->ties_pinned = fresh;
+    h->ties_cap = cap;
+    return SCT_OK;
+}
+
+// Start H2D + pass for chunk [first, first+n) of the caller's arrays.  Page-locked caller arrays are copied from
+// directly; pageable ones go through the slot's pinned staging (host threads).  The offsets travel as they are (the
+// kernels subtract the chunk's first offset b0), so neither path rewrites them.
+// `prev` = the slot holding the chunk before this one (still in flight): see enqueue_pass for the ordering.  The H2D copy
+// of this chunk (issued before the wait) and the D2H copies of the previous one overlap the kernels.
+int start_chunk(sct_handle *h, Slot &s, Slot *prev, const uint8_t *seg_bytes, const int64_t *off, int64_t first, int64_t n,
+                int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets) {
     const int64_t b0 = off[first], nbytes = off[first + n] - b0;
     if (nbytes < 0) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
     TRY(ensure_slot(h, s, n, nbytes));
     const double t0 = Trace::now();
-    if (nbytes > 0) par_memcpy(h->pool, s.h_bytes, seg_bytes + b0, (size_t)nbytes);
-    {
-        long long *dst = s.h_off;
-        const int64_t *src = off + first;
-        std::atomic<bool> bad(false);
-        par_ranges(h->pool, n + 1, 1 << 16, [&](int64_t a, int64_t b) {
-            bool mine = false;
-            for (int64_t i = a; i < b; ++i) {
-                dst[i] = src[i] - b0;
-                if (i < n && src[i + 1] < src[i]) mine = true;
-            }
-            if (mine) bad = true;
-        });
-        if (bad) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
+    const uint8_t *src_bytes = seg_bytes + b0;
+    const long long *src_off = reinterpret_cast<const long long *>(off + first);
+    if (!h->in_bytes_pinned && nbytes > 0) {
+        par_memcpy(h->pool, s.h_bytes, src_bytes, (size_t)nbytes);
+        src_bytes = s.h_bytes;
+    }
+    if (!h->in_off_pinned) {
+        par_memcpy(h->pool, s.h_off, src_off, (size_t)(n + 1) * sizeof(long long));
+        src_off = s.h_off;
     }
     g_tr.t_stage += Trace::now() - t0;
     s.n = n;
     s.nbytes = nbytes;
     s.first = first;
-    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
+    s.b0 = b0;
+    s.redo = false;
+    s.dst_min = h->out_min_pinned ? min_ed + first : s.h_min;
+    s.dst_nt = h->out_nt_pinned ? n_ties + first : s.h_nt;
+    s.dst_toff = h->out_toff_pinned ? reinterpret_cast<long long *>(tie_offsets + first) : s.h_toff;
+    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, src_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.d_off, src_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
     h->stats[3] += nbytes + (n + 1) * (int64_t)sizeof(long long);
     h->stats[5] += 1;
-    if (prev && prev->busy) CUDA_TRY(cudaStreamWaitEvent(s.stream, prev->ev_end, 0));
-    TRY(enqueue_pass(h, s, n));
+    TRY(enqueue_pass(h, s, n, prev));
     TRY(enqueue_result_copies(s));
     s.copies_enqueued = true;
     s.busy = true;
     return SCT_OK;
 }
 
-// Bring the results of slot s back and append them to the caller's arrays.
-int fetch_results(sct_handle *h, Slot &s, int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets, int64_t out_first,
-                  int64_t tie_base, int64_t *n_new_ties) {
+// Bring the tie ids of slot s back (into the call-wide pinned buffer, at the chunk's base) and hand the fixed-size
+// results that were staged — the caller's array was pageable — over to the caller's arrays.
+int fetch_results(sct_handle *h, Slot &s, int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets, int64_t *n_new_ties) {
     const int64_t n = s.n;
-    const long long total = n > 0 ? *s.h_total : 0;
+    const long long total = n > 0 ? s.h_total[0] : 0;
+    const long long base = n > 0 ? s.h_total[1] : 0;
     if (n > 0) {
         if (!s.copies_enqueued) TRY(enqueue_result_copies(s));
-        if (total > 0)
-            CUDA_TRY(cudaMemcpyAsync(s.h_ties, s.d_tieout, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        if (total > 0) {
+            TRY(ensure_ties(h, base + total, base));
+            CUDA_TRY(cudaMemcpyAsync(h->ties_pinned + base, s.d_tieout, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        }
         double t0 = Trace::now();
         CUDA_TRY(cudaStreamSynchronize(s.stream));
         g_tr.t_wait += Trace::now() - t0;
         t0 = Trace::now();
-        h->stats[4] += n * 8 + (n + 1) * 8 + total * 4;
-        par_memcpy(h->pool, min_ed + out_first, s.h_min, (size_t)n * sizeof(int));
-        par_memcpy(h->pool, n_ties + out_first, s.h_nt, (size_t)n * sizeof(int));
-        {
-            int64_t *dst = tie_offsets + out_first;
-            const long long *src = s.h_toff;
-            par_ranges(h->pool, n, 1 << 16, [&](int64_t a, int64_t b) {
-                for (int64_t i = a; i < b; ++i) dst[i] = tie_base + src[i];
-            });
-        }
-        if (total > 0) {
-            const size_t at = h->ties_host.size();
-            h->ties_host.resize(at + (size_t)total);
-            par_memcpy(h->pool, h->ties_host.data() + at, s.h_ties, (size_t)total * sizeof(int));
-        }
+        h->stats[4] += n * 8 + n * 8 + total * 4;
+        if (s.dst_min == s.h_min) par_memcpy(h->pool, min_ed + s.first, s.h_min, (size_t)n * sizeof(int));
+        if (s.dst_nt == s.h_nt) par_memcpy(h->pool, n_ties + s.first, s.h_nt, (size_t)n * sizeof(int));
+        if (s.dst_toff == s.h_toff) par_memcpy(h->pool, tie_offsets + s.first, s.h_toff, (size_t)n * sizeof(long long));
         g_tr.t_fetch += Trace::now() - t0;
     }
     *n_new_ties = total;
@@ -567,7 +632,9 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
     h->chunk_segs = segs;
     h->chunk_bytes = segs * 40;
     // streamed chunks are kept small enough that staging / copies of one chunk overlap the kernels of the other slot
-    h->stream_segs = std::min<int64_t>(segs, 1 << 18);
+    h->stream_segs = std::min<int64_t>(segs, 1 << 19);
+    // the table uploads above are pageable cudaMemcpy's on the legacy stream; the kernels run on non-blocking streams
+    CUDA_TRY(cudaDeviceSynchronize());
     *out = h;
     return SCT_OK;
 }
@@ -587,6 +654,8 @@ int sct_destroy(sct_handle *h) {
     dev_free(h->d_tabF); dev_free(h->d_tabR); dev_free(h->d_patF); dev_free(h->d_patR);
     dev_free(h->d_ovf_scratch); dev_free(h->d_flush);
     dev_free(h->d_boff); dev_free(h->d_ewords); dev_free(h->d_eids);
+    dev_free(h->d_tie_run);
+    host_free(h->ties_pinned);
     delete h->pool;
     delete h;
     return SCT_OK;
@@ -599,6 +668,7 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
         if (value < 1) return fail(SCT_E_ARG, "chunk_segments must be >= 1");
         h->chunk_segs = value;
         h->stream_segs = value;
+        h->ramp_segs = value;
         h->chunk_bytes = std::max<int64_t>(h->chunk_bytes, 64);
     } else if (k == "chunk_bytes") {
         if (value < 1) return fail(SCT_E_ARG, "chunk_bytes must be >= 1");
@@ -616,6 +686,12 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "seed_prefilter") {
         if (value != 0 && !h->seed_pre_ok) return fail(SCT_E_ARG, "seed_prefilter is not available for this barcode length / -mr");
         h->seed.prefilter = value != 0 ? 1 : 0;
+    } else if (k == "ramp_segments") {
+        if (value < 1) return fail(SCT_E_ARG, "ramp_segments must be >= 1");
+        h->ramp_segs = value;
+    } else if (k == "stream_segments") {
+        if (value < 1) return fail(SCT_E_ARG, "stream_segments must be >= 1");
+        h->stream_segs = std::min<int64_t>(value, h->chunk_segs);
     } else if (k == "seed_ctas_per_sm") {
         if (value < 1 || value > 32) return fail(SCT_E_ARG, "seed_ctas_per_sm must be 1..32");
         h->seed_ctas_per_sm = (int)value;
@@ -638,80 +714,118 @@ int sct_chunk_capacity(sct_handle *h, int64_t *max_segments, int64_t *max_bytes)
     return SCT_OK;
 }
 
+static int match_impl(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n, int32_t *min_ed,
+                      int32_t *n_ties, int64_t *tie_offsets, const int32_t **tie_ids, int64_t *n_tie_ids);
+
 int sct_match(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n, int32_t *min_ed,
               int32_t *n_ties, int64_t *tie_offsets, const int32_t **tie_ids, int64_t *n_tie_ids) {
+    const int rc = match_impl(h, seg_bytes, seg_offsets, n, min_ed, n_ties, tie_offsets, tie_ids, n_tie_ids);
+    if (rc != SCT_OK && h) {
+        // a call that failed half way leaves chunks in flight: drain them so that the handle stays usable (the error
+        // message of the failure is kept)
+        const std::string keep = g_err;
+        for (Slot &s : h->slot) {
+            if (s.stream) cudaStreamSynchronize(s.stream);
+            s.busy = s.copies_enqueued = s.redo = false;
+        }
+        cudaGetLastError();
+        g_err = keep;
+    }
+    return rc;
+}
+
+static int match_impl(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n, int32_t *min_ed,
+                      int32_t *n_ties, int64_t *tie_offsets, const int32_t **tie_ids, int64_t *n_tie_ids) {
     if (!h) return fail(SCT_E_ARG, "NULL handle");
     if (n < 0) return fail(SCT_E_ARG, "n < 0");
+    if (n > 0x7FFFFFF0ll) return fail(SCT_E_UNSUPPORTED, "more than 2^31 segments in one call");
     if (!seg_offsets || !tie_offsets || !tie_ids || !n_tie_ids || (n > 0 && (!min_ed || !n_ties)))
         return fail(SCT_E_ARG, "NULL argument");
     if (n > 0 && !seg_bytes && seg_offsets[n] > seg_offsets[0]) return fail(SCT_E_ARG, "seg_bytes is NULL");
     const double t_begin = Trace::now();
     g_tr.t_stage = g_tr.t_wait = g_tr.t_fetch = 0;
-    g_tr.t_check = Trace::now() - t_begin;
     CUDA_TRY(cudaSetDevice(h->device));
     memset(h->stats, 0, sizeof h->stats);
-    h->ties_host.clear();
+    memset(h->work, 0, sizeof h->work);
     h->staged = h->staged_ran = false;
+    // page-locked caller arrays (sct_host_alloc / sct_host_register / cudaHostAlloc) are copied from and to directly
+    const int64_t all_bytes = n > 0 ? seg_offsets[n] - seg_offsets[0] : 0;
+    h->in_bytes_pinned = n > 0 && all_bytes > 0 && is_pinned(seg_bytes + seg_offsets[0], (size_t)all_bytes);
+    h->in_off_pinned = n > 0 && is_pinned(seg_offsets, (size_t)(n + 1) * sizeof(int64_t));
+    h->out_min_pinned = n > 0 && is_pinned(min_ed, (size_t)n * sizeof(int32_t));
+    h->out_nt_pinned = n > 0 && is_pinned(n_ties, (size_t)n * sizeof(int32_t));
+    h->out_toff_pinned = n > 0 && is_pinned(tie_offsets, (size_t)(n + 1) * sizeof(int64_t));
+    g_tr.t_check = Trace::now() - t_begin;
+    NvtxRange nv_call("sct_match");
 
-    int64_t tie_base = 0;
+    int64_t tie_total = 0;
     int64_t first = 0, chunk = 0;
-    int64_t pending[2] = {-1, -1};   // chunk index held by each slot
     auto finish = [&](int si) -> int {
         Slot &s = h->slot[si];
         if (!s.busy) return SCT_OK;
+        NvtxRange nv("sct_match: wait + D2H ties");
         TRY(complete_pass(h, s));
         int64_t got = 0;
-        TRY(fetch_results(h, s, min_ed, n_ties, tie_offsets, s.first, tie_base, &got));
-        tie_base += got;
-        pending[si] = -1;
+        TRY(fetch_results(h, s, min_ed, n_ties, tie_offsets, &got));
+        tie_total += got;
         return SCT_OK;
     };
+    if (n > 0) {
+        TRY(ensure_slot(h, h->slot[0], 1, 1));
+        CUDA_TRY(cudaMemsetAsync(h->d_tie_run, 0, sizeof(long long), h->slot[0].stream));   // chunk 0 runs on this stream
+    }
+    // the first chunks are small so that the first kernel starts (and the pipeline fills) after a short copy
+    int64_t ramp = std::min<int64_t>(h->stream_segs, h->ramp_segs);
     while (first < n) {
-        int64_t cn = std::min<int64_t>(h->stream_segs, n - first);
+        int64_t cn = std::min<int64_t>(std::min(h->stream_segs, ramp), n - first);
+        ramp = std::min<int64_t>(h->stream_segs, ramp * 2);
         const int64_t limit = seg_offsets[first] + h->chunk_bytes;
         if (seg_offsets[first + cn] > limit) {
             const int64_t *e = std::upper_bound(seg_offsets + first, seg_offsets + first + cn + 1, limit);
             cn = std::max<int64_t>(1, (e - (seg_offsets + first)) - 1);
         }
-        const int si = (int)(chunk & 1);
-        TRY(finish(si));
-        TRY(start_chunk(h, h->slot[si], &h->slot[1 - si], seg_bytes, seg_offsets, first, cn));
-        pending[si] = chunk;
+        const int si = (int)(chunk % N_SLOTS);
+        TRY(finish(si));                 // the chunk that used this slot N_SLOTS chunks ago
+        {
+            NvtxRange nv("sct_match: stage + enqueue chunk");
+            Slot *prev = chunk > 0 ? &h->slot[(chunk - 1) % N_SLOTS] : nullptr;
+            TRY(start_chunk(h, h->slot[si], prev, seg_bytes, seg_offsets, first, cn, min_ed, n_ties, tie_offsets));
+        }
         first += cn;
         ++chunk;
     }
     // drain in chunk order
-    const int a = (pending[0] >= 0 && (pending[1] < 0 || pending[0] < pending[1])) ? 0 : 1;
-    TRY(finish(a));
-    TRY(finish(1 - a));
-    tie_offsets[n] = tie_base;
-    *tie_ids = h->ties_host.empty() ? nullptr : h->ties_host.data();
-    *n_tie_ids = tie_base;
+    for (int64_t c = std::max<int64_t>(0, chunk - N_SLOTS); c < chunk; ++c) TRY(finish((int)(c % N_SLOTS)));
+    tie_offsets[n] = tie_total;
+    *tie_ids = tie_total > 0 ? h->ties_pinned : nullptr;
+    *n_tie_ids = tie_total;
     if (g_tr.on)
-        fprintf(stderr, "[sct_match] n=%lld chunks=%lld total %.3f ms: check %.3f stage %.3f wait %.3f fetch %.3f\n",
+        fprintf(stderr, "[sct_match] n=%lld chunks=%lld total %.3f ms: check %.3f stage %.3f wait %.3f fetch %.3f pinned in %d%d out %d%d%d\n",
                 (long long)n, (long long)chunk, 1e3 * (Trace::now() - t_begin), 1e3 * g_tr.t_check, 1e3 * g_tr.t_stage,
-                1e3 * g_tr.t_wait, 1e3 * g_tr.t_fetch);
+                1e3 * g_tr.t_wait, 1e3 * g_tr.t_fetch, h->in_bytes_pinned, h->in_off_pinned, h->out_min_pinned,
+                h->out_nt_pinned, h->out_toff_pinned);
     return SCT_OK;
 }
 
 int sct_stage(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offsets, int64_t n) {
     if (!h || !seg_offsets || n < 0) return fail(SCT_E_ARG, "bad argument");
+    if (n > 0x7FFFFFF0ll) return fail(SCT_E_UNSUPPORTED, "more than 2^31 segments in one batch");
     CUDA_TRY(cudaSetDevice(h->device));
     Slot &s = h->slot[0];
     const int64_t nbytes = seg_offsets[n] - seg_offsets[0];
-    if (n > h->chunk_segs || nbytes > h->chunk_bytes)
-        return fail(SCT_E_ARG, "batch of %lld segments / %lld bytes exceeds the chunk capacity %lld / %lld",
-                    (long long)n, (long long)nbytes, (long long)h->chunk_segs, (long long)h->chunk_bytes);
+    if (nbytes < 0) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing");
+    // the resident batch may be larger than a streamed chunk (bench.py keeps a whole 10 M-segment shard in HBM): it only
+    // has to fit the device, which cudaMalloc decides
     TRY(ensure_slot(h, s, n, nbytes));
     const int64_t b0 = seg_offsets[0];
-    if (nbytes > 0) memcpy(s.h_bytes, seg_bytes + b0, (size_t)nbytes);
-    for (int64_t i = 0; i <= n; ++i) s.h_off[i] = seg_offsets[i] - b0;
-    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
+    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, seg_bytes + b0, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.d_off, seg_offsets, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
     CUDA_TRY(cudaStreamSynchronize(s.stream));
     s.n = n;
     s.nbytes = nbytes;
     s.first = 0;
+    s.b0 = b0;
+    s.redo = false;
     h->staged = true;
     h->staged_ran = false;
     return SCT_OK;
@@ -723,6 +837,10 @@ int sct_run_staged(sct_handle *h, float *pass_ms, float *match_kernel_ms) {
     CUDA_TRY(cudaSetDevice(h->device));
     Slot &s = h->slot[0];
     memset(h->stats, 0, sizeof h->stats);
+    memset(h->work, 0, sizeof h->work);
+    CUDA_TRY(cudaMemsetAsync(h->d_tie_run, 0, sizeof(long long), s.stream));
+    s.redo = false;
+    s.copies_enqueued = false;
     TRY(enqueue_pass(h, s, s.n));
     TRY(complete_pass(h, s));
     float a = 0.f, b = 0.f;
@@ -741,12 +859,62 @@ int sct_fetch_staged(sct_handle *h, int32_t *min_ed, int32_t *n_ties, int64_t *t
     if (!tie_offsets || !tie_ids || !n_tie_ids) return fail(SCT_E_ARG, "NULL argument");
     CUDA_TRY(cudaSetDevice(h->device));
     Slot &s = h->slot[0];
-    h->ties_host.clear();
+    const int64_t n = s.n;
     int64_t got = 0;
-    TRY(fetch_results(h, s, min_ed, n_ties, tie_offsets, 0, 0, &got));
-    tie_offsets[s.n] = got;
-    *tie_ids = h->ties_host.empty() ? nullptr : h->ties_host.data();
+    if (n > 0) {
+        // straight into the caller's arrays (cudaMemcpy handles pageable destinations)
+        CUDA_TRY(cudaMemcpyAsync(min_ed, s.d_min, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(n_ties, s.d_nt, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(tie_offsets, s.d_toff, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+        got = s.h_total[0];
+        if (got > 0) {
+            TRY(ensure_ties(h, got, 0));
+            CUDA_TRY(cudaMemcpyAsync(h->ties_pinned, s.d_tieout, (size_t)got * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        }
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+    }
+    tie_offsets[n] = got;
+    *tie_ids = got > 0 ? h->ties_pinned : nullptr;
     *n_tie_ids = got;
+    return SCT_OK;
+}
+
+int sct_host_alloc(size_t bytes, void **out) {
+    if (!out) return fail(SCT_E_ARG, "out is NULL");
+    *out = nullptr;
+    CUDA_TRY(cudaHostAlloc(out, std::max<size_t>(bytes, 64), cudaHostAllocPortable));
+    return SCT_OK;
+}
+
+int sct_host_free(void *p) {
+    if (p) CUDA_TRY(cudaFreeHost(p));
+    return SCT_OK;
+}
+
+int sct_host_register(void *p, size_t bytes) {
+    if (!p || bytes == 0) return fail(SCT_E_ARG, "bad argument");
+    CUDA_TRY(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return SCT_OK;
+}
+
+int sct_host_unregister(void *p) {
+    if (p) CUDA_TRY(cudaHostUnregister(p));
+    return SCT_OK;
+}
+
+const char *sct_kernel_name(sct_handle *h) {
+    if (!h) return "";
+    if (h->use_dp || h->path_override == 2) return "match_dp_kernel";
+    switch (fast_kind(h)) {
+        case 2: return "match_seed_kernel";
+        case 1: return "match_fast_kernel";
+        default: return "match_generic_kernel";
+    }
+}
+
+int sct_work_counters(sct_handle *h, int64_t counters[8]) {
+    if (!h || !counters) return fail(SCT_E_ARG, "NULL argument");
+    memcpy(counters, h->work, sizeof h->work);
     return SCT_OK;
 }
 

@@ -220,3 +220,62 @@ def write_fastq(path, read_bytes: np.ndarray, offsets: np.ndarray, first_index: 
                 f.write(b"".join(buf))
                 buf = []
         f.write(b"".join(buf))
+
+
+# ---- BASELINE configs[2]/[3]: ONE 10 M-segment input, defined block by block so that a rank can build just its shard ----
+BLOCK_SEGMENTS = 250_000
+BLOCK_SEED0 = 5000
+
+
+def concat_segments(parts):
+    """[(seg_bytes, offsets), ...] -> one (seg_bytes, offsets)."""
+    if len(parts) == 1:
+        return parts[0]
+    sb = np.concatenate([p[0] for p in parts])
+    offs, base = [np.zeros(1, dtype=np.int64)], 0
+    for p in parts:
+        offs.append(p[1][1:] + base)
+        base += int(p[1][-1])
+    return sb, np.concatenate(offs)
+
+
+def make_segments_range(barcodes: np.ndarray, first: int, last: int, block: int = BLOCK_SEGMENTS, seed0: int = BLOCK_SEED0):
+    """Segments [first, last) of the blocked workload: block b = make_segments(barcodes, block, seed0 + b).  The input is
+    the same for every sharding (rank r of N builds only the blocks its read range touches)."""
+    parts = []
+    for b in range(first // block, (max(last, first + 1) - 1) // block + 1):
+        sb, off = make_segments(barcodes, block, seed0 + b)
+        lo, hi = max(first, b * block) - b * block, min(last, (b + 1) * block) - b * block
+        if hi > lo:
+            parts.append((sb[off[lo]:off[hi]], off[lo:hi + 1] - off[lo]))
+    if not parts:
+        return np.zeros(0, dtype=np.uint8), np.zeros(1, dtype=np.int64)
+    return concat_segments(parts)
+
+
+def lengthen(seg_bytes: np.ndarray, offsets: np.ndarray, extra: int, seed: int):
+    """Every segment gets `extra` more random ACGT bases, split at random between its two ends (e.g. the 22-base bench
+    segments -> 40 bases: what `extract_lr_bc --num-bp-after 38` would cut)."""
+    rng = np.random.default_rng(seed + 611953)
+    n = offsets.shape[0] - 1
+    lens = np.diff(offsets)
+    new_off = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(lens + extra, out=new_off[1:])
+    out = ACGT[rng.integers(0, 4, size=int(new_off[-1]))]
+    left = rng.integers(0, extra + 1, size=n)
+    rid = np.repeat(np.arange(n), lens)
+    pos = np.arange(seg_bytes.size) - offsets[rid]
+    out[new_off[rid] + left[rid] + pos] = seg_bytes
+    return out, new_off
+
+
+def sprinkle_n(seg_bytes: np.ndarray, offsets: np.ndarray, frac: float, seed: int):
+    """A copy in which a fraction `frac` of the (non-empty) segments has one base replaced by 'N' (what a basecaller's
+    ambiguous call looks like: scored as 'A', and no match may start on the k bytes that cover it — SURVEY.md A.4)."""
+    rng = np.random.default_rng(seed + 32452843)
+    n = offsets.shape[0] - 1
+    lens = np.diff(offsets)
+    pick = np.nonzero((rng.random(n) < frac) & (lens > 0))[0]
+    out = seg_bytes.copy()
+    out[offsets[pick] + (rng.random(pick.size) * lens[pick]).astype(np.int64)] = ord("N")
+    return out

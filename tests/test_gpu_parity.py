@@ -197,6 +197,13 @@ def test_baseline_config_1m_seeded_equals_all_pairs_kernel(mr):
         _assert_same(m.match(sb, off), seeded)
     rows = int((seeded.min_ed >= 0).sum())
     assert rows == (887_994 if mr == 2 else 999_977)          # the bench's row counts for this seed
+    # ... and what the ORACLE gives (the C port of the reference's trie algorithm, itself pinned by reference outputs):
+    # the full million at -mr 2 (seconds on the box's cores), the first 100 k at -mr 3 (the port's DFS is ~15x slower there)
+    n = 1_000_000 if mr == 2 else 100_000
+    want = util.result_from_tuple(oracle.match(bc, sb[:off[n]], off[:n + 1], mr, threads=16, algo="trie"))
+    assert np.array_equal(seeded.min_ed[:n], want.min_ed) and np.array_equal(seeded.n_ties[:n], want.n_ties)
+    assert np.array_equal(seeded.tie_offsets[:n + 1], want.tie_offsets)
+    assert np.array_equal(seeded.tie_ids[:want.tie_ids.size], want.tie_ids)
 
 
 def test_baseline_config_10m_chunked_streaming_is_shard_invariant():
@@ -215,6 +222,12 @@ def test_baseline_config_10m_chunked_streaming_is_shard_invariant():
         parts = [m.match(p[0], p[1]) for p in parts_in]
     _assert_same(_lib.concat_results(parts), whole)
     assert int((parts[0].min_ed >= 0).sum()) == 887_994
+    # the first and the last million of the 10 M call against the oracle (C port of the reference's algorithm)
+    for i in (0, 9):
+        want = util.result_from_tuple(oracle.match(bc, parts_in[i][0], parts_in[i][1], 2, threads=16, algo="trie"))
+        lo, hi = i * 1_000_000, (i + 1) * 1_000_000
+        assert np.array_equal(whole.min_ed[lo:hi], want.min_ed) and np.array_equal(whole.n_ties[lo:hi], want.n_ties)
+        assert np.array_equal(whole.tie_ids[whole.tie_offsets[lo]:whole.tie_offsets[hi]], want.tie_ids)
 
 
 @pytest.mark.parametrize("name", ["ref100k.json", "ref10k_mr3.json"])
@@ -251,3 +264,57 @@ def test_error_codes():
             m.match(np.zeros(4, np.uint8), np.array([0, 3, 2], np.int64))   # decreasing offsets
         with pytest.raises(_lib.SctError):
             m.run_staged()                  # nothing staged
+
+
+def test_pinned_buffers_zero_copy_path_equals_staged_path():
+    """sct_match copies from / to page-locked caller arrays directly (no staging pass, offsets travel as they are and the
+    tie offsets leave the device in the call's numbering): same results as the pageable path, for any mix of pinned and
+    pageable arguments, a sub-range of a larger pinned array (non-zero first offset), many small chunks, reused buffers."""
+    rng = np.random.default_rng(31)
+    bc, sb, off = util.random_case(rng, 500, 20_000, bl=16, dirty=0.05, max_len=60)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, 2, threads=16, algo="dp"))
+    psb, poff = _lib.Pinned.copy_of(sb), _lib.Pinned.copy_of(off)
+    out = _lib.ResultBuffers(len(off) - 1)
+    with _lib.Matcher(bc, 2, 16) as m:
+        _assert_same(m.match(psb.array, poff.array, out=out, copy_ties=False), want)
+        _assert_same(m.match(psb.array, off, out=out), want)              # pinned bytes, pageable offsets
+        _assert_same(m.match(sb, poff.array), want)                       # pageable bytes, pinned offsets, pageable results
+        lo, hi = 5_000, 17_001                                            # a shard: offsets[lo] != 0
+        part = m.match(psb.array, poff.array[lo:hi + 1], out=out, copy_ties=False)
+        assert np.array_equal(part.min_ed, want.min_ed[lo:hi]) and np.array_equal(part.n_ties, want.n_ties[lo:hi])
+        assert np.array_equal(part.tie_offsets, want.tie_offsets[lo:hi + 1] - want.tie_offsets[lo])
+        assert np.array_equal(part.tie_ids, want.tie_ids[want.tie_offsets[lo]:want.tie_offsets[hi]])
+    with _lib.Matcher(bc, 2, 16, chunk_segments=333, chunk_bytes=1 << 20) as m:
+        _assert_same(m.match(psb.array, poff.array, out=out, copy_ties=False), want)
+        assert m.stats()["chunks"] >= 60
+    with _lib.Matcher(bc, 2, 16, stream_segments=4096, ramp_segments=64, tie_capacity_per_segment=0) as m:
+        _assert_same(m.match(psb.array, poff.array, out=out), want)       # tie buffer grows mid-call: pass redone
+    bad = _lib.Pinned.copy_of(off)
+    bad.array[100] = bad.array[99] - 5                                    # decreasing offsets are found on the device
+    with _lib.Matcher(bc, 2, 16) as m:
+        with pytest.raises(_lib.SctError) as e:
+            m.match(psb.array, bad.array, out=out)
+        assert e.value.code == -1
+        _assert_same(m.match(psb.array, poff.array, out=out), want)       # the handle stays usable
+    for x in (psb, poff, bad, out):
+        x.close()
+
+
+@pytest.mark.skipif(_lib.device_count() < 2, reason="needs two GPUs (gpurun --gpus 2)")
+def test_reads_sharded_over_two_gpus_equal_one_gpu():
+    """The product's own multi-GPU path (MatcherGroup: one handle + one host thread per GPU, contiguous read ranges,
+    concatenation in read order — the replacement of the reference's fan-out + merge, scTagger.py:688-716) on two
+    devices: identical to one device and to the oracle."""
+    bc = synth.make_barcodes(25_000, 1002)
+    sb, off = synth.make_segments(bc, 300_001, 2004)
+    one = _lib.match_segments(bc, sb, off, max_error=2, threads=16, devices=[0])
+    two = _lib.match_segments(bc, sb, off, max_error=2, threads=16, devices=[0, 1])
+    swapped = _lib.match_segments(bc, sb, off, max_error=2, threads=16, devices=[1, 0])
+    _assert_same(two, one)
+    _assert_same(swapped, one)
+    n = 20_000
+    want = util.result_from_tuple(oracle.match(bc, sb[:off[n]], off[:n + 1], 2, threads=16, algo="trie"))
+    assert np.array_equal(two.min_ed[:n], want.min_ed) and np.array_equal(two.tie_ids[:want.tie_ids.size], want.tie_ids)
+    g = _lib.device_count()
+    allg = _lib.match_segments(bc, sb, off, max_error=2, threads=16, devices=g)
+    _assert_same(allg, one)
