@@ -281,7 +281,7 @@ def useful_fraction(work, K, bl, kern_s, peak_lop3, pre_pairs):
     return {"automaton_steps": steps, "lop3_lane_ops": lop3, "shift_lane_ops": steps * (K + 1),
             "frac": lop3 / kern_s / peak_lop3 if kern_s > 0 else None,
             "probes": work["probes"], "verifications": work["verifications"], "prechecks": work["prechecks"],
-            "segments_set_up": work["segments_set_up"],
+            "windows_set_up": work["windows_set_up"], "wide_segments": work["wide_segments"],
             "definition": "(verifications x bl + prechecks x pre-check characters) x (2K+1) LOP3 lane-ops / kernel time / "
                           "LOP3 peak; bucket probes, queueing and per-segment set-up count as overhead, not as useful work"}
 

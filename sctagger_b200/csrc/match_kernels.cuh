@@ -46,6 +46,8 @@ struct Counters {                    // device-side cursors, zeroed before every
     // live work counters of the seeded kernels (bench.py's roofline.useful): bucket probes, full verifications,
     // pre-checks, segments set up
     unsigned long long n_probe, n_verify, n_precheck, n_setup;
+    // seeded mode: segments that are longer than one 31-base window or hold a non-ACGT byte (windowed seeded kernel)
+    unsigned int n_wide, cur_wide;
 };
 
 struct MatchParams {
@@ -60,6 +62,8 @@ struct MatchParams {
     const uint8_t *colinfo;          // per raw byte: (2*code) | v-bits << 3 (generic segments only)
     const uint8_t *segflag;
     const int *fast_list, *gen_list;
+    const int *wide_list;            // seeded mode: segments for the windowed variant of the seeded kernel
+    const unsigned long long *pk;    // seeded mode: 2-bit packed text, segment i at word (byte offset >> 5) + i
     int *ovf_list;
     Counters *ctr;
     int *min_ed, *n_ties;
@@ -526,6 +530,69 @@ __global__ void __launch_bounds__(256) prep_kernel(const uint8_t *__restrict__ b
     }
     segflag[i] = flag;
     gen_list[atomicAdd(&ctr->n_gen, 1u)] = i;
+}
+
+// PREP kernel of the seeded mode: one thread per segment, ANY length, ANY bytes.  Writes
+//   * pk: the text as 2-bit codes (non-ACGT bytes as A = 0, map_char scTagger.py:512-516), 32 bases per 64-bit word,
+//     segment i starting at word (byte offset >> 5) + i (always enough room: the next segment starts at least
+//     ceil(L / 32) words later), zero-padded inside its last word;
+//   * colinfo: per byte (2 * code) | v-bits << 3 — the start-state row D0 of SURVEY.md Appendix A.4 folded into one bit
+//     per error level (bit d = [D0 <= d]); the windowed seeded kernel reads the v bits, the overflow re-run all of it;
+//   * the work list: clean segments of <= fast_max bases -> fast_list (one window, every start allowed), the others
+//     (longer, or with a non-ACGT byte) -> wide_list (overlapping 31-base windows, start states from colinfo).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) prep_seed_kernel(const uint8_t *__restrict__ bytes, const long long *__restrict__ off,
+                                                        long long b0, long long nbytes, int n_seg, int bl, int K, int kpre,
+                                                        int fast_max, unsigned long long *__restrict__ pk,
+                                                        uint8_t *__restrict__ colinfo, uint8_t *__restrict__ segflag,
+                                                        int *__restrict__ fast_list, int *__restrict__ wide_list,
+                                                        Counters *__restrict__ ctr, int *__restrict__ min_ed,
+                                                        int *__restrict__ n_ties) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_seg) return;
+    const long long o = off[i] - b0;
+    long long L = off[i + 1] - b0 - o;
+    if (L < 0 || o < 0 || o + L > nbytes) {   // the caller's offsets are not non-decreasing inside the chunk: the call fails
+        atomicAdd(&ctr->n_bad, 1u);
+        L = 0;
+    }
+    if (L < bl - K) {   // cannot hold a barcode within K edits: the reference emits no row (scTagger.py:681)
+        segflag[i] = SEG_SHORT;
+        min_ed[i] = -1;
+        n_ties[i] = 0;
+        return;
+    }
+    unsigned long long *dst = pk + (o >> 5) + i;
+    unsigned long long w = 0;
+    bool clean = true;
+    int prev = 1000;
+    uint8_t flag = 0;
+    for (long long j = 0; j <= L; ++j) {
+        bool valid = j + kpre <= L;
+        for (int q = 0; valid && q < kpre; ++q) valid = base_code(bytes[o + j + q]) >= 0;
+        prev = valid ? 0 : min(prev + 1, 1000);
+        uint32_t vb = 0;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) vb |= (prev <= d ? 1u : 0u) << d;
+        if (j == 0) {
+            flag = (prev == 0) ? SEG_START0 : 0;
+        } else {
+            const int cc = base_code(bytes[o + j - 1]);
+            const int c = cc < 0 ? 0 : cc;
+            clean = clean && cc >= 0;
+            colinfo[o + j - 1] = (uint8_t)((2 * c) | (vb << 3));
+            const int at = (int)((j - 1) & 31);
+            w |= (unsigned long long)c << (2 * at);
+            if (at == 31) {
+                dst[(j - 1) >> 5] = w;
+                w = 0;
+            }
+        }
+    }
+    if (L & 31) dst[L >> 5] = w;
+    segflag[i] = flag;
+    if (clean && L <= fast_max) fast_list[atomicAdd(&ctr->n_fast, 1u)] = i;
+    else wide_list[atomicAdd(&ctr->n_wide, 1u)] = i;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

@@ -33,7 +33,8 @@ struct Slot {
     // device
     uint8_t *d_bytes = nullptr, *d_colinfo = nullptr, *d_rec = nullptr, *d_segflag = nullptr;
     long long *d_off = nullptr;
-    int *d_fast = nullptr, *d_gen = nullptr, *d_ovf = nullptr, *d_dp = nullptr;
+    int *d_fast = nullptr, *d_gen = nullptr, *d_ovf = nullptr, *d_dp = nullptr, *d_wide = nullptr;
+    int64_t pk_words = 0;
     unsigned long long *d_pk = nullptr;
     Counters *d_ctr = nullptr;
     int *d_min = nullptr, *d_nt = nullptr;
@@ -76,7 +77,8 @@ struct sct_handle {
     int host_threads = 1;        // worker threads for staging / un-staging (from -t, capped)
     HostPool *pool = nullptr;
     int tie_per_seg = 8;
-    int seed_ctas_per_sm = 6;
+    int seed_ctas_per_sm = 5;               // = what __launch_bounds__(256, 5) and 35 KB of shared memory let be resident
+    int seed_fast_max = SEED_MAX_LEN;       // longest clean segment of the one-window kernel (option: 0 sends everything to the windowed one)
     bool seed_pre_ok = false;
     uint32_t *d_ovf_scratch = nullptr;
     int ovf_blocks = 16, ovf_cap = 0;
@@ -100,8 +102,9 @@ int free_slot(Slot &s) {
     host_free(s.h_bytes); host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
     host_free(s.h_ctr); host_free(s.h_total);
     dev_free(s.d_bytes); dev_free(s.d_colinfo); dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off);
-    dev_free(s.d_fast); dev_free(s.d_gen); dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_ctr);
+    dev_free(s.d_fast); dev_free(s.d_gen); dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_ctr); dev_free(s.d_wide);
     dev_free(s.d_pk);
+    s.pk_words = 0;
     dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart); dev_free(s.d_tiebuf); dev_free(s.d_tieout);
     dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_total);
     s.cap_segs = s.cap_bytes = 0;
@@ -140,7 +143,7 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
         dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off); dev_free(s.d_fast); dev_free(s.d_gen);
         dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart);
-        dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_pk);
+        dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_wide);
         s.cap_segs = 0;
         CUDA_TRY(cudaMallocHost(&s.h_off, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMallocHost(&s.h_min, c * sizeof(int)));
@@ -148,12 +151,12 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         CUDA_TRY(cudaMallocHost(&s.h_toff, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_rec, (size_t)c * REC_BYTES));
         CUDA_TRY(cudaMalloc(&s.d_segflag, (size_t)c));
-        CUDA_TRY(cudaMalloc(&s.d_pk, (size_t)c * sizeof(unsigned long long)));
         CUDA_TRY(cudaMalloc(&s.d_off, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_fast, c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_gen, c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_ovf, c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_dp, c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_wide, c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_min, c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_nt, c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_tstart, c * sizeof(unsigned int)));
@@ -174,6 +177,14 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         CUDA_TRY(cudaMalloc(&s.d_colinfo, (size_t)c + 64));
         s.cap_bytes = c;
     }
+    // 2-bit packed text of the seeded mode: segment i starts at word (byte offset >> 5) + i
+    const int64_t pkw = s.cap_bytes / 32 + s.cap_segs + 4;
+    if (pkw > s.pk_words) {
+        dev_free(s.d_pk);
+        s.pk_words = 0;
+        CUDA_TRY(cudaMalloc(&s.d_pk, (size_t)pkw * sizeof(unsigned long long)));
+        s.pk_words = pkw;
+    }
     return SCT_OK;
 }
 
@@ -193,6 +204,8 @@ MatchParams make_params(sct_handle *h, Slot &s) {
     p.fast_list = s.d_fast;
     p.gen_list = s.d_gen;
     p.ovf_list = s.d_ovf;
+    p.wide_list = s.d_wide;
+    p.pk = s.d_pk;
     p.ctr = s.d_ctr;
     p.min_ed = s.d_min;
     p.n_ties = s.d_nt;
@@ -211,9 +224,15 @@ int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 non
     if (fast == 2) {
         // seeded kernel: small static shared memory, many resident warps (latency-bound gathers + verification)
         const int grid = h->sm_count * h->seed_ctas_per_sm;
-        if (h->bl == 16 && h->seed.prefilter) match_seed_kernel<K, true, true><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
-        else if (h->bl == 16) match_seed_kernel<K, true, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
-        else match_seed_kernel<K, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed, s.d_pk);
+        if (h->bl == 16 && h->seed.prefilter) match_seed_kernel<K, true, true, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
+        else if (h->bl == 16) match_seed_kernel<K, true, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
+        else match_seed_kernel<K, false, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
+        CUDA_TRY(cudaGetLastError());
+        // the segments the one-window kernel does not take (longer than 31 bases, or with a non-ACGT byte)
+        const int wgrid = h->sm_count * 4;
+        if (h->bl == 16 && h->seed.prefilter) match_seed_kernel<K, true, true, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
+        else if (h->bl == 16) match_seed_kernel<K, true, false, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
+        else match_seed_kernel<K, false, false, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
         CUDA_TRY(cudaGetLastError());
         CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
     } else if (fast == 1) {
@@ -230,8 +249,10 @@ int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 non
     // the generic kernels share the handle's overflow scratch with the other slot's chunk, the finalize advances the
     // running tie base: both stay behind that chunk's finalize
     if (after && fast) CUDA_TRY(cudaStreamWaitEvent(s.stream, after, 0));
-    match_generic_kernel<K><<<h->sm_count * 4, GEN_THREADS, 0, s.stream>>>(p, 0);
-    CUDA_TRY(cudaGetLastError());
+    if (fast != 2) {                 // in seeded mode prep_seed_kernel leaves the generic list empty
+        match_generic_kernel<K><<<h->sm_count * 4, GEN_THREADS, 0, s.stream>>>(p, 0);
+        CUDA_TRY(cudaGetLastError());
+    }
     match_generic_kernel<K><<<h->ovf_blocks, GEN_THREADS, 0, s.stream>>>(p, 1);
     CUDA_TRY(cudaGetLastError());
     return SCT_OK;
@@ -260,10 +281,14 @@ int enqueue_pass(sct_handle *h, Slot &s, int64_t n, Slot *prev = nullptr) {
     CUDA_TRY(cudaMemsetAsync(s.d_ctr, 0, sizeof(Counters), s.stream));
     int launches = 0;
     if (n > 0) {
-        prep_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.d_bytes, s.d_off, s.b0, s.nbytes, (int)n, h->bl, h->K, h->kpre, path,
-                                                                     fk == 2 ? SEED_MAX_LEN : FAST_MAX_LEN,
-                                                                     fk == 2 ? s.d_pk : nullptr, s.d_rec, s.d_colinfo, s.d_segflag, s.d_fast, s.d_gen,
-                                                                     s.d_dp, s.d_ctr, s.d_min, s.d_nt);
+        if (fk == 2 && path == 0)
+            prep_seed_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.d_bytes, s.d_off, s.b0, s.nbytes, (int)n, h->bl, h->K, h->kpre,
+                                                                              h->seed_fast_max, s.d_pk, s.d_colinfo, s.d_segflag,
+                                                                              s.d_fast, s.d_wide, s.d_ctr, s.d_min, s.d_nt);
+        else
+            prep_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.d_bytes, s.d_off, s.b0, s.nbytes, (int)n, h->bl, h->K, h->kpre, path,
+                                                                         FAST_MAX_LEN, nullptr, s.d_rec, s.d_colinfo, s.d_segflag, s.d_fast,
+                                                                         s.d_gen, s.d_dp, s.d_ctr, s.d_min, s.d_nt);
         CUDA_TRY(cudaGetLastError());
         ++launches;
         CUDA_TRY(cudaEventRecord(s.ev_k0, s.stream));
@@ -287,7 +312,7 @@ int enqueue_pass(sct_handle *h, Slot &s, int64_t n, Slot *prev = nullptr) {
                 default: TRY(launch_match<3>(h, s, p, fk, chained ? prev->ev_end : nullptr)); break;
             }
             if (!fk) CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
-            launches += fk ? 3 : 2;
+            launches += fk == 2 ? 3 : (fk ? 3 : 2);
         }
         if (chained) CUDA_TRY(cudaStreamWaitEvent(s.stream, prev->ev_end, 0));
         const int nb = (int)((n + SCAN_BLOCK - 1) / SCAN_BLOCK);
@@ -341,6 +366,7 @@ int complete_pass(sct_handle *h, Slot &s) {
             h->work[1] += (int64_t)s.h_ctr->n_verify;
             h->work[2] += (int64_t)s.h_ctr->n_precheck;
             h->work[3] += (int64_t)s.h_ctr->n_setup;
+            h->work[4] += (int64_t)s.h_ctr->n_wide;
             s.redo = false;
             return SCT_OK;
         }
@@ -692,6 +718,9 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "stream_segments") {
         if (value < 1) return fail(SCT_E_ARG, "stream_segments must be >= 1");
         h->stream_segs = std::min<int64_t>(value, h->chunk_segs);
+    } else if (k == "seed_fast_max") {   // test hook: 0 routes every segment through the windowed variant
+        if (value < 0 || value > SEED_MAX_LEN) return fail(SCT_E_ARG, "seed_fast_max must be 0..%d", SEED_MAX_LEN);
+        h->seed_fast_max = (int)value;
     } else if (k == "seed_ctas_per_sm") {
         if (value < 1 || value > 32) return fail(SCT_E_ARG, "seed_ctas_per_sm must be 1..32");
         h->seed_ctas_per_sm = (int)value;

@@ -66,13 +66,25 @@ __device__ __forceinline__ uint32_t and_or(uint32_t a, uint32_t b, uint32_t c) {
 // Exact level (0..K, or K+1) of one barcode word against one strand of the text.  tab_a is the shared-memory address
 // (128-byte aligned) of that strand's PAIR table: entry e = c0 | c1 << 2 holds {Eq[c0], Eq[c1]}, so one LDS.64 feeds
 // two steps of the automaton and the character extract is one shift + one LOP3 per two barcode characters.
-template <int K, bool BL16>
-__device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t tab_a, uint32_t full, uint32_t two) {
+// INIT: the level-d start state is read from shared memory (v_a: 4 words, bit j = a match may start at text position j
+// with d edits already spent — segments with restricted starts) instead of "every position".
+template <int K, bool BL16, bool INIT>
+__device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t tab_a, uint32_t full, uint32_t two, uint32_t v_a) {
     uint32_t R[K + 1], S[K + 1];
+    if (INIT) {
+        uint32_t v[4];
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(v_a));
 #pragma unroll
-    for (int d = 0; d <= K; ++d) {
-        R[d] = full;
-        S[d] = full << 1;
+        for (int d = 0; d <= K; ++d) {
+            R[d] = v[d];
+            S[d] = v[d] << 1;
+        }
+    } else {
+#pragma unroll
+        for (int d = 0; d <= K; ++d) {
+            R[d] = full;
+            S[d] = full << 1;
+        }
     }
     auto row = [&](uint32_t eq) {
         uint32_t r = S[0] & eq;
@@ -197,9 +209,19 @@ __device__ __forceinline__ int sort_unique(uint32_t *list, uint32_t *tmp, int co
     return out;
 }
 
-template <int K, bool BL16, bool PRE>
-__global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const MatchParams p, const SeedIndex ix,
-                                                                  const unsigned long long *__restrict__ pk) {
+// GEN = false: clean segments of <= 31 bases (fast_list), one window, every start allowed, reverse strand scored as the
+//               forward barcode against revcomp(T).
+// GEN = true:  any other segment (wide_list): overlapping windows of <= 31 bases, window w starting at base w * stride,
+//               stride = 32 - bl - K, so that every substring of <= bl + K bases — every alignment within K edits — lies
+//               inside one window; min over windows = min over the segment, ties are the union (sort_unique drops the
+//               duplicates of overlapping windows).  Non-ACGT bytes are scored as A (pk) and restrict where a match may
+//               START (reference: the -t prefix rule): the level-d start state of the automaton is
+//               the window's slice of [D0 <= d] (v bits of colinfo) instead of "everywhere".  A start restriction on T is
+//               an END restriction on revcomp(T), so here the reverse strand is scored as revcomp(barcode) (the entry's
+//               second word) against the forward text.  Seeds and the anchored pre-check ignore the restriction: they stay
+//               necessary conditions.
+template <int K, bool BL16, bool PRE, bool GEN>
+__global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(const MatchParams p, const SeedIndex ix) {
     constexpr int NSLOT = 2 * (K + 1) * 32;
     // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
     __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
@@ -214,6 +236,8 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
     __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
     __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
     __shared__ __align__(16) uint32_t s_init[33][8];           // pre-check start states by boundary: R0 S0 R1 S1 R2 S2 R3 S3
+    __shared__ __align__(16) uint32_t s_v[SEED_WARPS][4];      // GEN: start states of the window per level
+    __shared__ unsigned long long s_cnt[SEED_WARPS][4];        // work counters: probes, verifications, candidates, windows
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x < 33) {
@@ -225,26 +249,57 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
             s_init[b][2 * d + 1] = r << 1;
         }
     }
+    if (lane < 4) s_cnt[warp][lane] = 0ull;
     __syncthreads();
     // opaque copies: ptxas otherwise re-derives these shared-memory addresses from SR_CgaCtaId in every loop iteration
     uint32_t init_a = smem_u32(&s_init[0][0]);
     asm volatile("mov.u32 %0, %0;" : "+r"(init_a));
     uint32_t *prefix = s_prefix[warp], *start = s_start[warp], *list = s_list[warp], *tmp = s_tmp[warp];
     const uint32_t pair_a = smem_u32(&s_pair[warp][0][0]);
-    const unsigned int n_fast = p.ctr->n_fast;
+    const uint32_t v_a = smem_u32(&s_v[warp][0]);
+    const unsigned int n_items = GEN ? p.ctr->n_wide : p.ctr->n_fast;
+    unsigned int *cursor = GEN ? &p.ctr->cur_wide : &p.ctr->cur_fast;
+    const int *items = GEN ? p.wide_list : p.fast_list;
     const int bl = p.bl;
     const int P = ix.n_pieces;
+    const int stride = 32 - bl - K;                                      // GEN: window step (>= 13 for bl <= 16, K <= 3)
     const uint32_t lt_mask = (1u << lane) - 1u;
-    unsigned long long n_cand = 0;
 
     for (;;) {
         unsigned int idx = 0;
-        if (lane == 0) idx = atomicAdd(&p.ctr->cur_fast, 1u);
+        if (lane == 0) idx = atomicAdd(cursor, 1u);
         idx = __shfl_sync(FULL, idx, 0);
-        if (idx >= n_fast) break;
-        const int seg = p.fast_list[idx];
-        const int n = (int)(p.seg_off[seg + 1] - p.seg_off[seg]);
-        const unsigned long long fw = __ldg(pk + seg);
+        if (idx >= n_items) break;
+        const int seg = items[idx];
+        const long long so = p.seg_off[seg] - p.b0;
+        const int n_total = (int)(p.seg_off[seg + 1] - p.b0 - so);
+        const unsigned long long *pw = p.pk + (so >> 5) + seg;
+        int best = K + 1, count = 0;
+        uint32_t *queue = s_queue[warp];
+        for (int ws = 0;; ws += stride) {                                // windows (exactly one when !GEN)
+        int n;
+        unsigned long long fw;
+        if (!GEN) {
+            n = n_total;
+            fw = __ldg(pw);
+        } else {
+            n = min(SEED_MAX_LEN, n_total - ws);
+            const unsigned long long a = __ldg(pw + (ws >> 5)), b = __ldg(pw + (ws >> 5) + 1);
+            const int sh = 2 * (ws & 31);
+            fw = sh ? ((a >> sh) | (b << (64 - sh))) : a;
+            fw &= (1ull << (2 * n)) - 1ull;
+            // start states: bit j of level d = [D0[ws + j] <= d], j = 0..n
+            uint32_t vb = 0;
+            if (lane <= n) {
+                const int pos = ws + lane;
+                vb = pos == 0 ? ((p.segflag[seg] & SEG_START0) ? 0xFu : 0u) : (uint32_t)(p.colinfo[so + pos - 1] >> 3);
+            }
+#pragma unroll
+            for (int d = 0; d < 4; ++d) {
+                const uint32_t m = __ballot_sync(FULL, (vb >> d) & 1u);
+                if (lane == d) s_v[warp][d] = m;
+            }
+        }
         // reverse complement of the packed text: complement, reverse the 2-bit groups, drop the unused tail
         unsigned long long rc = __brevll(~fw);
         rc = ((rc & 0x5555555555555555ull) << 1) | ((rc >> 1) & 0x5555555555555555ull);
@@ -267,6 +322,7 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
         // bucket ranges of every (strand, piece, position); the non-empty ones become slots, prefix-summed in order
         uint32_t total = 0;
         int n_slots = 0;
+        uint32_t n_probe = 0;
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
             const unsigned long long text = s ? fw : rc;               // strand 0 first
@@ -276,6 +332,7 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
                 if (q < P) {
                     const int o = ix.piece_off[q], ln = ix.piece_len[q];
                     const int lo = max(0, o - K), hi = min(n - ln, n - (bl - o) + K);
+                    n_probe += (uint32_t)max(0, hi - lo + 1);
                     if (lane >= lo && lane <= hi) {
                         const uint32_t h = (uint32_t)(text >> (2 * lane)) & ((1u << (2 * ln)) - 1u);
                         const uint32_t *b = ix.boff + ix.boff_base[q] + h;
@@ -319,16 +376,20 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
             }
             __syncwarp();
         }
-        n_cand += total;
         const uint32_t full = (n >= 31) ? 0xFFFFFFFFu : ((1u << (n + 1)) - 1u);
-        int best = K + 1, count = 0;
+        uint32_t n_ver = 0;
         // exact level of up to 32 queued candidates (lane < cnt), folded into the running (minimum, tie list)
         auto verify = [&](uint32_t item, bool valid) {
             int level = K + 1;
             const uint32_t entry = item & 0x7FFFFFFFu, strand = item >> 31;
             if (valid) {
-                const uint32_t word = __ldg(&ix.ewords[entry].x);
-                level = seed_verify<K, BL16>(word, bl, pair_a + strand * 128u, full, ix.two);
+                if (GEN) {
+                    const uint2 words = __ldg(ix.ewords + entry);
+                    level = seed_verify<K, BL16, true>(strand ? words.x : words.y, bl, pair_a + 128u, full, ix.two, v_a);
+                } else {
+                    const uint32_t word = __ldg(&ix.ewords[entry].x);
+                    level = seed_verify<K, BL16, false>(word, bl, pair_a + strand * 128u, full, ix.two, 0u);
+                }
             }
             const unsigned hit = __ballot_sync(FULL, level <= K);
             if (hit) {
@@ -347,7 +408,6 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
                 }
             }
         };
-        uint32_t *queue = s_queue[warp];
         int qn = 0;
         int cur = 0;                                                    // slot holding candidate t0 (warp-uniform)
         for (uint32_t t0 = 0; t0 < total; t0 += 32) {
@@ -382,18 +442,33 @@ __global__ void __launch_bounds__(SEED_THREADS, 5) match_seed_kernel(const Match
                 __syncwarp();
                 queue[lane] = rest;
                 qn -= 32;
+                n_ver += 32u;
                 __syncwarp();
             }
         }
         __syncwarp();
         if (qn > 0) verify(lane < qn ? queue[lane] : 0u, lane < qn);
+        n_ver += (uint32_t)qn;
+        if (lane == 0) {
+            s_cnt[warp][0] += n_probe;
+            s_cnt[warp][1] += n_ver;
+            s_cnt[warp][2] += total;
+            s_cnt[warp][3] += 1ull;
+        }
         __syncwarp();
+        if (!GEN || ws + SEED_MAX_LEN >= n_total) break;
+        }
+        // more hits than the list holds (in GEN mode possibly only duplicates from overlapping windows): exact re-run
         if (count <= SEED_LIST_CAP) count = sort_unique(list, tmp, count, lane);
         store_result(p, seg, lane, K, best, count, list, SEED_LIST_CAP, true);
         __syncwarp();
     }
-    if (lane == 0 && n_cand) {
-        atomicAdd(&p.ctr->n_cand, n_cand);
+    if (lane == 0) {
+        if (s_cnt[warp][2]) atomicAdd(&p.ctr->n_cand, s_cnt[warp][2]);
+        if (s_cnt[warp][0]) atomicAdd(&p.ctr->n_probe, s_cnt[warp][0]);
+        if (s_cnt[warp][1]) atomicAdd(&p.ctr->n_verify, s_cnt[warp][1]);
+        if (s_cnt[warp][3]) atomicAdd(&p.ctr->n_setup, s_cnt[warp][3]);
+        if (PRE && s_cnt[warp][2]) atomicAdd(&p.ctr->n_precheck, s_cnt[warp][2]);
     }
 }
 

@@ -103,3 +103,76 @@ def match_segment(bc_codes, index, seg, K, stats=None):
     if best > K:
         return -1, []
     return best, sorted(ties)
+
+
+def start_levels(seg, kpre):
+    """D0 of SURVEY.md Appendix A.4 for positions 0..n: 0 where a match may start (the next kpre bytes exist and are all
+    upper-case ACGT — the reference's -t prefix rule), else the previous value + 1.  Mirrors prep_seed_kernel."""
+    n = len(seg)
+    out, prev = [], 1000
+    for j in range(n + 1):
+        valid = j + kpre <= n and all(b in CODE for b in seg[j:j + kpre])
+        prev = 0 if valid else min(prev + 1, 1000)
+        out.append(prev)
+    return out
+
+
+def verify_restricted(word_codes, text_codes, K, init):
+    """verify() with per-level start states: init[d] bit j = a match may start at text position j with d edits spent."""
+    n = len(text_codes)
+    full = (1 << (n + 1)) - 1
+    eq = [0, 0, 0, 0]
+    for j, c in enumerate(text_codes):
+        eq[c] |= 1 << (j + 1)
+    M32 = 0xFFFFFFFF
+    R = list(init[:K + 1])
+    for c in word_codes:
+        e = eq[int(c)]
+        S = [(r << 1) & M32 for r in R]
+        nR = [S[0] & e]
+        for d in range(1, K + 1):
+            nR.append(((S[d] & e) | R[d - 1] | S[d - 1] | ((nR[d - 1] << 1) & M32)) & M32)
+        R = nR
+    for d in range(K + 1):
+        if R[d] & full:
+            return d
+    return K + 1
+
+
+def match_segment_windowed(bc_codes, index, seg, K, kpre):
+    """Twin of match_seed_kernel<GEN = true>: ANY segment.  Non-ACGT bytes are scored as A; overlapping windows of <= 31
+    bases, window step 32 - bl - K; per window the pigeonhole seeds of both strands (restriction ignored: necessary
+    condition) and a verification on the FORWARD text with the window's slice of the start levels — the reverse strand as
+    revcomp(barcode).  -> (min_ed or -1, sorted unique tie ids)"""
+    pieces, tables = index
+    bl = bc_codes.shape[1]
+    n_total = len(seg)
+    if n_total < bl - K:
+        return -1, []
+    codes = [CODE.get(b, 0) for b in seg]
+    d0 = start_levels(seg, kpre)
+    stride = 32 - bl - K
+    best, ties = K + 1, set()
+    ws = 0
+    while True:
+        n = min(31, n_total - ws)
+        fwd = codes[ws:ws + n]
+        rc = [3 - c for c in reversed(fwd)]
+        init = [sum(1 << j for j in range(n + 1) if d0[ws + j] <= d) for d in range(4)]
+        for strand, text in ((0, rc), (1, fwd)):
+            for (o, ln), table in zip(pieces, tables):
+                lo, hi = max(0, o - K), min(n - ln, n - (bl - o) + K)
+                for j in range(lo, hi + 1):
+                    for b in table.get(pack(text[j:j + ln]), ()):
+                        word = bc_codes[b] if strand else [3 - int(c) for c in reversed(bc_codes[b])]
+                        lv = verify_restricted(word, fwd, K, init)
+                        if lv < best:
+                            best, ties = lv, set()
+                        if lv == best and lv <= K:
+                            ties.add((b << 1) | strand)
+        if ws + 31 >= n_total:
+            break
+        ws += stride
+    if best > K:
+        return -1, []
+    return best, sorted(ties)

@@ -72,3 +72,17 @@ def test_cli_stdout_and_barcode_length_assertion(tmp_path):
     assert r.returncode == 0 and r.stdout == util.read_maybe_gz(os.path.join(d, c["out"]))
     r = subprocess.run(base + ["-bl", "15"], cwd=util.ROOT, capture_output=True)     # scTagger.py:760-761
     assert r.returncode != 0 and b"AssertionError" in r.stderr
+
+
+def test_sctagger_py_entry_script_has_the_reference_command_line():
+    """./scTagger.py is the reference's script name (scTagger.py:864-865): same sub-commands and flags."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scTagger.py"), "match_trie", "-h"], capture_output=True, text=True)
+    assert r.returncode == 0
+    for flag in ("-lr", "-sr", "-mr", "-bl", "-m", "-t", "-p", "-o"):
+        assert flag in r.stdout
+    r = subprocess.run([sys.executable, os.path.join(root, "scTagger.py"), "match_trie", "-lr", "x"], capture_output=True, text=True)
+    assert r.returncode == 2 and "-sr" in r.stderr          # argparse: a required flag is missing

@@ -68,6 +68,56 @@ def test_random_against_oracle(seed):
         _assert_same(_lib.match_segments(bc, sb, off, max_error=mr, threads=t, path=3), want)   # all-pairs tile kernel
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_long_and_dirty_segments_on_the_windowed_seeded_kernel(seed):
+    """Segments of any length and with non-ACGT bytes stay on the seeded path (overlapping 31-base windows, start states
+    from the reference's -t prefix rule): bit-exact with the oracle, nothing left to the all-pairs generic kernel."""
+    rng = np.random.default_rng(4100 + seed)
+    bl = [16, 16, 16, 12, 16, 14, 16, 16][seed]
+    mr = [2, 3, 1, 2, 2, 3, 0, 2][seed]
+    t = [16, 16, 4, 17, 1, 64, 16, 5][seed]
+    dirty = [0.0, 0.4, 0.4, 0.3, 0.5, 0.3, 0.4, 1.0][seed]
+    lo, hi = [(20, 64), (30, 200), (14, 90), (10, 120), (31, 33), (28, 60), (16, 400), (40, 46)][seed]
+    bc, sb, off = util.long_case(rng, [600, 400, 999, 300, 700, 350, 500, 800][seed], 1200, bl=bl, min_len=lo, max_len=hi,
+                                 dirty=dirty)
+    want = oracle.match(bc, sb, off, mr, threads=t, algo="dp")
+    with _lib.Matcher(bc, mr, t) as m:
+        got = m.match(sb, off)
+        st, wk = m.stats(), m.work_counters()
+    _assert_same(got, want)
+    if bl // (mr + 1) >= 4:          # seeded configurations (every piece >= 4 characters; the others use the tile kernel)
+        assert st["generic_segments"] == 0 and wk["wide_segments"] > 0
+    # the same input with every segment forced through the windowed variant
+    _assert_same(_lib.match_segments(bc, sb, off, max_error=mr, threads=t, seed_fast_max=0), want)
+
+
+def test_window_seams_every_position():
+    """One barcode (and its reverse complement) planted at every position of a 120-base segment, with an N walking
+    next to it: every seam of the overlapping windows and every start restriction next to a window edge."""
+    rng = np.random.default_rng(99)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    bc = acgt[rng.integers(0, 4, size=(64, 16))]
+    base = acgt[rng.integers(0, 4, size=120)]
+    segs = []
+    for at in range(0, 105):
+        for variant in range(4):
+            s = base.copy()
+            core = bc[at % 64].copy()
+            if variant & 1:
+                core = np.array([{65: 84, 67: 71, 71: 67, 84: 65}[int(x)] for x in core[::-1]], np.uint8)
+            s[at:at + 16] = core
+            if variant & 2:
+                s[max(0, at - 1 - (at % 3))] = ord("N")
+                s[min(119, at + 16 + (at % 2))] = ord("n")
+            segs.append(s.tobytes())
+    off = np.zeros(len(segs) + 1, np.int64)
+    np.cumsum([len(x) for x in segs], out=off[1:])
+    sb = np.frombuffer(b"".join(segs), np.uint8)
+    for mr, t in ((2, 16), (3, 64), (1, 4)):
+        want = oracle.match(bc, sb, off, mr, threads=t, algo="dp")
+        _assert_same(_lib.match_segments(bc, sb, off, max_error=mr, threads=t), want)
+
+
 @pytest.mark.parametrize("bl,mr", [(17, 2), (24, 3), (32, 4), (16, 4), (16, 5)])
 def test_dp_kernel_ranges(bl, mr):
     """barcode length 17..32 or max_error > 3 run on the DP kernel."""

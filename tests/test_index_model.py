@@ -37,3 +37,21 @@ def test_piece_layout_is_disjoint_and_has_k_plus_1_pieces():
                 assert o >= end and 1 <= ln <= 8
                 end = o + ln
             assert end <= bl
+
+
+@pytest.mark.parametrize("bl,K,t", [(16, 2, 16), (16, 3, 64), (16, 1, 4), (12, 2, 17), (14, 3, 1), (16, 2, 5)])
+def test_windowed_model_equals_oracle_on_long_and_dirty_segments(bl, K, t):
+    """The windowed variant (any length, non-ACGT bytes, start restrictions of the -t prefix rule) against the oracle."""
+    rng = np.random.default_rng(bl * 1000 + K * 10 + t)
+    bc, sb, off = util.long_case(rng, 150, 260, bl=bl, min_len=bl - K - 1, max_len=110, dirty=0.5)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, K, threads=t, algo="dp"))
+    kpre = 0
+    while 4 ** kpre < t:
+        kpre += 1
+    codes = np.vectorize(im.CODE.get)(bc).astype(np.uint8)
+    index = im.build_index(codes, K)
+    raw = sb.tobytes()
+    for r in range(len(off) - 1):
+        got = im.match_segment_windowed(codes, index, raw[off[r]:off[r + 1]], K, kpre)
+        assert got[0] == want.min_ed[r], r
+        assert got[1] == want.ties(r).tolist(), r

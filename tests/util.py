@@ -81,3 +81,39 @@ def random_case(rng, n_bc, n_seg, bl=16, dirty=0.0, max_len=40, lower=False):
     np.cumsum([len(s) for s in segs], out=offsets[1:])
     seg_bytes = np.frombuffer(b"".join(segs), dtype=np.uint8).copy()
     return bc, seg_bytes, offsets
+
+
+def long_case(rng, n_bc, n_seg, bl=16, min_len=20, max_len=200, dirty=0.0, plant=2):
+    """Random barcodes + LONG random segments with up to `plant` mutated barcodes (either strand) planted anywhere,
+    optionally with non-ACGT bytes: exercises the windowed seeded kernel (window seams, start restrictions)."""
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    bc = acgt[rng.integers(0, 4, size=(n_bc, bl))]
+    comp = {65: 84, 67: 71, 71: 67, 84: 65}
+    segs = []
+    for _ in range(n_seg):
+        L = int(rng.integers(min_len, max_len + 1))
+        s = list(acgt[rng.integers(0, 4, size=L)])
+        for _p in range(int(rng.integers(0, plant + 1))):
+            core = [int(x) for x in bc[int(rng.integers(0, n_bc))]]
+            for _e in range(int(rng.integers(0, 4))):
+                k = int(rng.integers(0, 3))
+                if k == 0:
+                    core[int(rng.integers(0, len(core)))] = int(acgt[rng.integers(0, 4)])
+                elif k == 1:
+                    core.insert(int(rng.integers(0, len(core) + 1)), int(acgt[rng.integers(0, 4)]))
+                else:
+                    del core[int(rng.integers(0, len(core)))]
+            if rng.random() < 0.5:
+                core = [comp[x] for x in reversed(core)]
+            if len(core) <= L:
+                at = int(rng.integers(0, L - len(core) + 1))
+                s[at:at + len(core)] = core
+        if dirty and rng.random() < dirty:
+            for _d in range(int(rng.integers(1, 4))):
+                i = int(rng.integers(0, len(s)))
+                s[i] = ord("N") if rng.random() < 0.7 else (int(s[i]) | 0x20)
+        segs.append(bytes(int(x) for x in s))
+    offsets = np.zeros(n_seg + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in segs], out=offsets[1:])
+    seg_bytes = np.frombuffer(b"".join(segs), dtype=np.uint8).copy()
+    return bc, seg_bytes, offsets
