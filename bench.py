@@ -273,17 +273,18 @@ def result_digest(res):
     return h.hexdigest()
 
 
-def useful_fraction(work, K, bl, kern_s, peak_lop3, pre_pairs):
-    """Automaton arithmetic actually performed (device counters of this run): every automaton step is 2K+1 LOP3 on the
-    ALU pipe (+ K+1 shifts issued as IMAD on the FMA pipe, reported separately)."""
-    steps = work["verifications"] * bl + work["prechecks"] * 2 * pre_pairs
-    lop3 = steps * (2 * K + 1)
-    return {"automaton_steps": steps, "lop3_lane_ops": lop3, "shift_lane_ops": steps * (K + 1),
-            "frac": lop3 / kern_s / peak_lop3 if kern_s > 0 else None,
+def useful_fraction(work, kern_s, peak_lop3, n_segments):
+    """Automaton arithmetic actually performed, from the device counters of THIS run: every automaton step of a phase
+    with error bound k is 2k+1 LOP3 on the ALU pipe (+ k+1 shifts issued as IMAD on the FMA pipe); the kernel sums
+    steps x (2k+1) over its full verifications and anchored pre-checks."""
+    lop3 = work["automaton_lop3_lane_ops"]
+    return {"lop3_lane_ops": lop3, "frac": lop3 / kern_s / peak_lop3 if kern_s > 0 else None,
             "probes": work["probes"], "verifications": work["verifications"], "prechecks": work["prechecks"],
-            "windows_set_up": work["windows_set_up"], "wide_segments": work["wide_segments"],
-            "definition": "(verifications x bl + prechecks x pre-check characters) x (2K+1) LOP3 lane-ops / kernel time / "
-                          "LOP3 peak; bucket probes, queueing and per-segment set-up count as overhead, not as useful work"}
+            "phases_run": work["phases_run"], "phases_per_segment": work["phases_run"] / max(n_segments, 1),
+            "wide_segments": work["wide_segments"],
+            "definition": "sum over full verifications and anchored pre-checks of automaton steps x (2k+1) LOP3 lane-ops "
+                          "(k = error bound of the phase) / kernel time / LOP3 peak; bucket probes, queueing and "
+                          "per-segment set-up count as overhead, not as useful work"}
 
 
 def issued_from_ncu(name, live_kernel_ms, segments_live):
@@ -345,7 +346,8 @@ def secondary_match(name, bc, sb, off, max_error, peak_lop3, steps=5, oracle_n=0
            "e2e": {"value": n / e2e_s, "ms": 1e3 * e2e_s, "equals_resident": bool(same),
                    "h2d_bytes": st2["h2d_bytes"], "d2h_bytes": st2["d2h_bytes"]},
            "roofline": {"frac": algo / kern_s / peak_lop3,
-                        "useful": useful_fraction(work, max_error, 16, kern_s, peak_lop3, 4 if max_error >= 3 else 3)["frac"],
+                        "useful": useful_fraction(work, kern_s, peak_lop3, n)["frac"],
+                        "phases_per_segment": work["phases_run"] / max(n, 1),
                         "candidates_per_segment": st["seed_candidates"] / max(n, 1)},
            "rows": int((res.min_ed >= 0).sum()), "sha256": result_digest(res),
            "fast_segments": st["fast_segments"], "generic_segments": st["generic_segments"]}
@@ -514,7 +516,7 @@ def _main():
     kern_s = kern_ms * 1e-3 / a.steps
     achieved = algo_ops / kern_s
     kernel_name = m.kernel_name() if hasattr(m, "kernel_name") else "match_seed_kernel"
-    useful = useful_fraction(work, a.max_error, 16, kern_s, peak_lop3, 4 if a.max_error >= 3 else 3)
+    useful = useful_fraction(work, kern_s, peak_lop3, n)
     issued = issued_from_ncu(f"r02_ncu_{kernel_name.split('<')[0]}_K{a.max_error}.txt", kern_ms / a.steps, n)
     for x in (psb, poff, out):
         x.close()

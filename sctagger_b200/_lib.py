@@ -182,7 +182,7 @@ def _as_u8(a):
 
 STAT_NAMES = ("launches", "fast_segments", "generic_segments", "h2d_bytes", "d2h_bytes", "chunks",
               "dp_segments", "seed_candidates")
-WORK_NAMES = ("probes", "verifications", "prechecks", "windows_set_up", "wide_segments", "reserved5", "reserved6",
+WORK_NAMES = ("probes", "verifications", "prechecks", "phases_run", "wide_segments", "automaton_lop3_lane_ops", "reserved6",
               "reserved7")
 
 

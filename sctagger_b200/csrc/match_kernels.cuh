@@ -48,6 +48,7 @@ struct Counters {                    // device-side cursors, zeroed before every
     unsigned long long n_probe, n_verify, n_precheck, n_setup;
     // seeded mode: segments that are longer than one 31-base window or hold a non-ACGT byte (windowed seeded kernel)
     unsigned int n_wide, cur_wide;
+    unsigned long long n_lop3;       // automaton steps x (2k+1): the LOP3 lane-ops of the seeded kernels' automata, per lane
 };
 
 struct MatchParams {

@@ -67,9 +67,12 @@ struct sct_handle {
     int n_tiles = 0;
     bool clean_barcodes = true, use_dp = false, fast_ok = false, seed_ok = false;
     int path_override = 0;       // 0 auto, 1 force generic, 2 force dp, 3 force the tile (all-pairs) kernel
-    uint32_t *d_boff = nullptr, *d_eids = nullptr;
-    uint2 *d_ewords = nullptr;
-    SeedIndex seed{};
+    uint32_t *d_boff[3] = {nullptr, nullptr, nullptr}, *d_eids[3] = {nullptr, nullptr, nullptr};
+    uint2 *d_ewords[3] = {nullptr, nullptr, nullptr};
+    SeedIndex seed_by_k[4] = {};  // index of error bound k (k = 0 only when -mr 0), built in sct_create for k = 1..K
+    bool seed_pre_by_k[4] = {false, false, false, false};   // the anchored pre-check is possible for this bound
+    int seed_deepening = 1;       // option: search error bounds 1, 2, .. K in turn and stop at the first hit
+    int seed_prefilter_opt = -1;  // option seed_prefilter: -1 auto (per phase, by expected bucket size), 0 off, 1 on where possible
     size_t fast_smem = 0;
     int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
     int64_t stream_segs = 0;                    // segments per streamed chunk of sct_match (<= chunk_segs)
@@ -218,21 +221,47 @@ MatchParams make_params(sct_handle *h, Slot &s) {
     return p;
 }
 
+// The phases of one launch: error bounds 1 .. K with iterative deepening (0 only for -mr 0), else K alone.  The anchored
+// pre-check runs in a phase when it is possible there and — unless the option forces it — when the phase's buckets hold
+// enough candidates for the filter to pay (expected entries per probe >= 2).  -> any phase uses the pre-check
+bool seed_phases(const sct_handle *h, SeedPhases &ph) {
+    const int K = h->K;
+    const int first = (h->seed_deepening && K >= 1) ? 1 : K;
+    ph.n_phases = K - first + 1;
+    bool any = false;
+    for (int k = first; k <= K; ++k) {
+        SeedIndex &ix = ph.ph[k - first];
+        ix = h->seed_by_k[k];
+        ix.first_phase = k == first ? 1 : 0;
+        int min_len = 99;
+        for (int q = 0; q < ix.n_pieces; ++q) min_len = std::min(min_len, ix.piece_len[q]);
+        const double per_probe = (double)h->B / (double)(1ull << (2 * min_len));
+        bool on = h->seed_pre_by_k[k] && h->bl == 16;
+        if (h->seed_prefilter_opt == 0) on = false;
+        else if (h->seed_prefilter_opt < 0) on = on && per_probe >= 2.0;
+        ix.prefilter = on ? 1 : 0;
+        any = any || on;
+    }
+    return any;
+}
+
 template <int K>
 int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 none, 1 tile kernel, 2 seeded kernel */,
                  cudaEvent_t after /* everything behind the main kernel waits for this event (may be null) */) {
     if (fast == 2) {
         // seeded kernel: small static shared memory, many resident warps (latency-bound gathers + verification)
         const int grid = h->sm_count * h->seed_ctas_per_sm;
-        if (h->bl == 16 && h->seed.prefilter) match_seed_kernel<K, true, true, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
-        else if (h->bl == 16) match_seed_kernel<K, true, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
-        else match_seed_kernel<K, false, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
+        SeedPhases ph;
+        const bool any_pre = seed_phases(h, ph);
+        if (h->bl == 16 && any_pre) match_seed_kernel<K, true, true, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, ph);
+        else if (h->bl == 16) match_seed_kernel<K, true, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, ph);
+        else match_seed_kernel<K, false, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, ph);
         CUDA_TRY(cudaGetLastError());
         // the segments the one-window kernel does not take (longer than 31 bases, or with a non-ACGT byte)
         const int wgrid = h->sm_count * 4;
-        if (h->bl == 16 && h->seed.prefilter) match_seed_kernel<K, true, true, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
-        else if (h->bl == 16) match_seed_kernel<K, true, false, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
-        else match_seed_kernel<K, false, false, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, h->seed);
+        if (h->bl == 16 && any_pre) match_seed_kernel<K, true, true, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, ph);
+        else if (h->bl == 16) match_seed_kernel<K, true, false, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, ph);
+        else match_seed_kernel<K, false, false, true><<<wgrid, SEED_THREADS, 0, s.stream>>>(p, ph);
         CUDA_TRY(cudaGetLastError());
         CUDA_TRY(cudaEventRecord(s.ev_k1, s.stream));
     } else if (fast == 1) {
@@ -367,6 +396,7 @@ int complete_pass(sct_handle *h, Slot &s) {
             h->work[2] += (int64_t)s.h_ctr->n_precheck;
             h->work[3] += (int64_t)s.h_ctr->n_setup;
             h->work[4] += (int64_t)s.h_ctr->n_wide;
+            h->work[5] += (int64_t)s.h_ctr->n_lop3;
             s.redo = false;
             return SCT_OK;
         }
@@ -577,58 +607,63 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
         CUDA_TRY(cudaMemcpy(h->d_tabR, tR.data(), tab_words * 4, cudaMemcpyHostToDevice));
         h->fast_smem = (size_t)h->n_tiles * TILE_BYTES + (size_t)FAST_WARPS * FAST_LIST_CAP * 4 + 16;
         h->fast_ok = h->clean_barcodes && h->fast_smem <= (size_t)h->max_smem_optin;
-        // seeded kernel: K+1 disjoint pieces (longer pieces last, capped at 8 characters), one bucket table per piece
+        // seeded kernel: per error bound k = 1..K (0 for -mr 0) an index of k+1 disjoint pieces (longer pieces last, capped
+        // at 8 characters), one bucket table per piece
         {
-            const int P = max_error + 1;
-            const int base = bl / P, extra = bl % P;
-            int o = 0, min_len = 99;
-            size_t boff_words = 0;
-            h->seed.n_pieces = P;
-            for (int q = 0; q < P && q < SEED_MAX_PIECES; ++q) {
-                const int ln = base + (q >= P - extra ? 1 : 0);
-                h->seed.piece_off[q] = o;
-                h->seed.piece_len[q] = std::min(ln, 8);
-                h->seed.boff_base[q] = (int)boff_words;
-                boff_words += ((size_t)1 << (2 * h->seed.piece_len[q])) + 1;
-                min_len = std::min(min_len, h->seed.piece_len[q]);
-                o += ln;
+            std::vector<uint32_t> code((size_t)B), rcode((size_t)B);
+            for (int b = 0; b < B; ++b) {
+                uint32_t w = 0;
+                for (int i = 0; i < bl; ++i) w |= (uint32_t)patF[(size_t)b * bl + i] << (2 * i);
+                code[b] = w;
+                uint32_t rw = 0;                         // reverse complement, same packing
+                for (int i = 0; i < bl; ++i) rw |= (uint32_t)(3 - patF[(size_t)b * bl + (bl - 1 - i)]) << (2 * i);
+                rcode[b] = rw;
             }
-            // below 4 characters per piece nearly every barcode is a candidate: the all-pairs tile kernel is faster there
-            h->seed_ok = h->clean_barcodes && P <= SEED_MAX_PIECES && min_len >= 4 && B > 0 &&
-                         (size_t)P * B < ((size_t)1 << 31);          // entry index shares a word with the strand bit
-            // anchored pre-check (seed_precheck): per piece the side of the barcode with more characters left
-            bool pre_ok = true;
-            for (int q = 0; q < P && q < SEED_MAX_PIECES; ++q) {
-                const int po = h->seed.piece_off[q], ln = h->seed.piece_len[q];
-                const int right = bl - (po + ln), left = po;
-                const bool go_left = left > right;
-                const int avail = go_left ? left : right;
-                const int pairs = seed_pre_pairs(max_error);
-                if (avail < 2 * pairs) pre_ok = false;
-                h->seed.pre[q] = (uint32_t)(go_left ? bl - po : po + ln) | ((go_left ? 1u : 0u) << 5) |
-                                 ((uint32_t)pairs << 6) | ((uint32_t)ln << 9);
-            }
-            h->seed.prefilter = (bl == 16 && pre_ok) ? 1 : 0;
-            h->seed_pre_ok = h->seed.prefilter != 0;
-            if (h->seed_ok) {
-                std::vector<uint32_t> boff(boff_words, 0u), ei((size_t)P * B), code((size_t)B), rcode((size_t)B);
-                std::vector<uint2> ew((size_t)P * B + 32, make_uint2(0u, 0u));   // + 32: the kernel's branch-free tail reads past the last bucket
-                for (int b = 0; b < B; ++b) {
-                    uint32_t w = 0;
-                    for (int i = 0; i < bl; ++i) w |= (uint32_t)patF[(size_t)b * bl + i] << (2 * i);
-                    code[b] = w;
-                    uint32_t rw = 0;                         // reverse complement, same packing (meaningful for bl = 16)
-                    for (int i = 0; i < bl; ++i) rw |= (uint32_t)(3 - patF[(size_t)b * bl + (bl - 1 - i)]) << (2 * i);
-                    rcode[b] = rw;
+            h->seed_ok = h->clean_barcodes && B > 0;
+            for (int k = (max_error >= 1 ? 1 : 0); k <= max_error && h->seed_ok; ++k) {
+                SeedIndex &ix = h->seed_by_k[k];
+                const int P = k + 1;
+                const int base = bl / P, extra = bl % P;
+                int o = 0, min_len = 99;
+                size_t boff_words = 0;
+                ix.n_pieces = P;
+                for (int q = 0; q < P && q < SEED_MAX_PIECES; ++q) {
+                    const int ln = base + (q >= P - extra ? 1 : 0);
+                    ix.piece_off[q] = o;
+                    ix.piece_len[q] = std::min(ln, 8);
+                    ix.boff_base[q] = (int)boff_words;
+                    boff_words += ((size_t)1 << (2 * ix.piece_len[q])) + 1;
+                    min_len = std::min(min_len, ix.piece_len[q]);
+                    o += ln;
                 }
+                // below 4 characters per piece nearly every barcode is a candidate: the all-pairs tile kernel is faster there
+                if (!(P <= SEED_MAX_PIECES && min_len >= 4 && (size_t)P * B < ((size_t)1 << 31))) {   // entry index shares a word with the strand bit
+                    h->seed_ok = false;
+                    break;
+                }
+                // anchored pre-check (seed_precheck): per piece the side of the barcode with more characters left
+                bool pre_ok = true;
                 for (int q = 0; q < P; ++q) {
-                    const int po = h->seed.piece_off[q], ln = h->seed.piece_len[q];
+                    const int po = ix.piece_off[q], ln = ix.piece_len[q];
+                    const int right = bl - (po + ln), left = po;
+                    const bool go_left = left > right;
+                    const int avail = go_left ? left : right;
+                    const int pairs = seed_pre_pairs(k);
+                    if (avail < 2 * pairs) pre_ok = false;
+                    ix.pre[q] = (uint32_t)(go_left ? bl - po : po + ln) | ((go_left ? 1u : 0u) << 5) |
+                                ((uint32_t)pairs << 6) | ((uint32_t)ln << 9);
+                }
+                h->seed_pre_by_k[k] = bl == 16 && pre_ok;
+                std::vector<uint32_t> boff(boff_words, 0u), ei((size_t)P * B);
+                std::vector<uint2> ew((size_t)P * B + 32, make_uint2(0u, 0u));   // + 32: the kernel's branch-free tail reads past the last bucket
+                for (int q = 0; q < P; ++q) {
+                    const int po = ix.piece_off[q], ln = ix.piece_len[q];
                     const uint32_t mask = (ln == 16) ? 0xFFFFFFFFu : ((1u << (2 * ln)) - 1u);
-                    uint32_t *bo = boff.data() + h->seed.boff_base[q];
+                    uint32_t *bo = boff.data() + ix.boff_base[q];
                     const size_t nb = (size_t)1 << (2 * ln);
                     for (int b = 0; b < B; ++b) ++bo[((code[b] >> (2 * po)) & mask) + 1];
                     bo[0] = (uint32_t)((size_t)q * B);
-                    for (size_t k = 1; k <= nb; ++k) bo[k] += bo[k - 1];
+                    for (size_t kk = 1; kk <= nb; ++kk) bo[kk] += bo[kk - 1];
                     std::vector<uint32_t> cur(bo, bo + nb);
                     for (int b = 0; b < B; ++b) {            // ascending barcode id inside a bucket
                         const uint32_t at = cur[(code[b] >> (2 * po)) & mask]++;
@@ -636,17 +671,21 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
                         ei[at] = (uint32_t)b;
                     }
                 }
-                CUDA_TRY(cudaMalloc(&h->d_boff, boff.size() * 4));
-                CUDA_TRY(cudaMalloc(&h->d_ewords, ew.size() * sizeof(uint2)));
-                CUDA_TRY(cudaMalloc(&h->d_eids, ei.size() * 4));
-                CUDA_TRY(cudaMemcpy(h->d_boff, boff.data(), boff.size() * 4, cudaMemcpyHostToDevice));
-                CUDA_TRY(cudaMemcpy(h->d_ewords, ew.data(), ew.size() * sizeof(uint2), cudaMemcpyHostToDevice));
-                CUDA_TRY(cudaMemcpy(h->d_eids, ei.data(), ei.size() * 4, cudaMemcpyHostToDevice));
-                h->seed.boff = h->d_boff;
-                h->seed.ewords = h->d_ewords;
-                h->seed.eids = h->d_eids;
-                h->seed.two = 2u;
+                const int di = k == 0 ? 0 : k - 1;
+                CUDA_TRY(cudaMalloc(&h->d_boff[di], boff.size() * 4));
+                CUDA_TRY(cudaMalloc(&h->d_ewords[di], ew.size() * sizeof(uint2)));
+                CUDA_TRY(cudaMalloc(&h->d_eids[di], ei.size() * 4));
+                CUDA_TRY(cudaMemcpy(h->d_boff[di], boff.data(), boff.size() * 4, cudaMemcpyHostToDevice));
+                CUDA_TRY(cudaMemcpy(h->d_ewords[di], ew.data(), ew.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+                CUDA_TRY(cudaMemcpy(h->d_eids[di], ei.data(), ei.size() * 4, cudaMemcpyHostToDevice));
+                ix.boff = h->d_boff[di];
+                ix.ewords = h->d_ewords[di];
+                ix.eids = h->d_eids[di];
+                ix.two = 2u;
+                ix.prefilter = 0;
+                ix.first_phase = 0;
             }
+            h->seed_pre_ok = h->seed_ok && h->seed_pre_by_k[max_error];
         }
         h->ovf_cap = h->n_tiles * 512;
         CUDA_TRY(cudaMalloc(&h->d_ovf_scratch, (size_t)h->ovf_blocks * GEN_WARPS * h->ovf_cap * sizeof(uint32_t)));
@@ -679,7 +718,7 @@ int sct_destroy(sct_handle *h) {
     }
     dev_free(h->d_tabF); dev_free(h->d_tabR); dev_free(h->d_patF); dev_free(h->d_patR);
     dev_free(h->d_ovf_scratch); dev_free(h->d_flush);
-    dev_free(h->d_boff); dev_free(h->d_ewords); dev_free(h->d_eids);
+    for (int i = 0; i < 3; ++i) { dev_free(h->d_boff[i]); dev_free(h->d_ewords[i]); dev_free(h->d_eids[i]); }
     dev_free(h->d_tie_run);
     host_free(h->ties_pinned);
     delete h->pool;
@@ -710,8 +749,10 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
             return fail(SCT_E_UNSUPPORTED, "the tile kernel needs ACGT-only barcodes and a table that fits shared memory");
         h->path_override = (int)value;
     } else if (k == "seed_prefilter") {
-        if (value != 0 && !h->seed_pre_ok) return fail(SCT_E_ARG, "seed_prefilter is not available for this barcode length / -mr");
-        h->seed.prefilter = value != 0 ? 1 : 0;
+        if (value > 0 && !h->seed_pre_ok) return fail(SCT_E_ARG, "seed_prefilter is not available for this barcode length / -mr");
+        h->seed_prefilter_opt = value < 0 ? -1 : (value != 0 ? 1 : 0);   // -1 auto, 0 off, 1 on wherever possible
+    } else if (k == "seed_deepening") {     // 1 (default): error bounds 1..K in turn, stop at the first hit; 0: bound K only
+        h->seed_deepening = value != 0 ? 1 : 0;
     } else if (k == "ramp_segments") {
         if (value < 1) return fail(SCT_E_ARG, "ramp_segments must be >= 1");
         h->ramp_segs = value;

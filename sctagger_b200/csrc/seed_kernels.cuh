@@ -46,6 +46,7 @@ struct SeedIndex {
     // bit 5 = extend to the left of the seed, bits 6-8 = pair lookups (0 = no pre-check), bits 9-13 = piece length
     uint32_t pre[SEED_MAX_PIECES];
     int prefilter;                         // 1 = run the anchored pre-check (option "seed_prefilter")
+    int first_phase;                       // 1 = this phase builds the segment's Eq tables (the first one that runs)
 };
 __host__ __device__ constexpr int seed_pre_pairs(int K) { return K >= 3 ? 4 : 3; }   // 6 characters; 8 at -mr 3
 constexpr int SEED_QUEUE_CAP = 64;         // pre-check survivors waiting for a full verification, per warp
@@ -209,74 +210,43 @@ __device__ __forceinline__ int sort_unique(uint32_t *list, uint32_t *tmp, int co
     return out;
 }
 
+// Per-warp views of the kernel's shared memory.
+struct SeedWarp {
+    uint32_t *prefix, *start, *aux, *queue, *map, *list, *tmp, *v;
+    uint2 *pair;                 // [2][16]
+    unsigned long long *cnt;     // work counters of the warp
+    uint32_t pair_a, v_a, init_a;
+};
+constexpr int SEED_MAPW = 128;   // slot-start bitmap: candidates 1..4096 of a window
+
+// One PHASE of the search for one segment: every (barcode, strand) within KP edits, exactly (pigeonhole seeds of the
+// phase's index -> anchored pre-check -> full verification), folded into (best, count, list).  best = KP + 1 when there
+// is none.
 // GEN = false: clean segments of <= 31 bases (fast_list), one window, every start allowed, reverse strand scored as the
 //               forward barcode against revcomp(T).
 // GEN = true:  any other segment (wide_list): overlapping windows of <= 31 bases, window w starting at base w * stride,
-//               stride = 32 - bl - K, so that every substring of <= bl + K bases — every alignment within K edits — lies
-//               inside one window; min over windows = min over the segment, ties are the union (sort_unique drops the
+//               stride = 32 - bl - KP, so that every substring of <= bl + KP bases — every alignment within KP edits —
+//               lies inside one window; min over windows = min over the segment, ties are the union (sort_unique drops the
 //               duplicates of overlapping windows).  Non-ACGT bytes are scored as A (pk) and restrict where a match may
 //               START (reference: the -t prefix rule): the level-d start state of the automaton is
 //               the window's slice of [D0 <= d] (v bits of colinfo) instead of "everywhere".  A start restriction on T is
 //               an END restriction on revcomp(T), so here the reverse strand is scored as revcomp(barcode) (the entry's
 //               second word) against the forward text.  Seeds and the anchored pre-check ignore the restriction: they stay
 //               necessary conditions.
-template <int K, bool BL16, bool PRE, bool GEN>
-__global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(const MatchParams p, const SeedIndex ix) {
-    constexpr int NSLOT = 2 * (K + 1) * 32;
-    // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
-    __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
-    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket - index of its first candidate
-    __shared__ uint32_t s_aux[SEED_WARPS][NSLOT];              // strand << 8 | pre-check operands of the slot (see seed_precheck)
-    __shared__ uint32_t s_queue[SEED_WARPS][SEED_QUEUE_CAP];   // pre-check survivors: entry | strand << 31
-    // bit t-1 = "a slot starts at candidate t": word j is the slot-start mask of candidates 32j+1 .. 32j+32.  Used when
-    // the segment's candidates fit (always at -mr <= 2 on real data); otherwise the mask is derived from s_prefix.
-    constexpr int MAPW = (K <= 2) ? 128 : 0;
-    __shared__ uint32_t s_map[SEED_WARPS][MAPW > 0 ? MAPW : 1];
-    __shared__ __align__(128) uint2 s_pair[SEED_WARPS][2][16]; // per strand: entry c0 | c1 << 2 = {Eq[c0], Eq[c1]}
-    __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
-    __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
-    __shared__ __align__(16) uint32_t s_init[33][8];           // pre-check start states by boundary: R0 S0 R1 S1 R2 S2 R3 S3
-    __shared__ __align__(16) uint32_t s_v[SEED_WARPS][4];      // GEN: start states of the window per level
-    __shared__ unsigned long long s_cnt[SEED_WARPS][4];        // work counters: probes, verifications, candidates, windows
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    if (threadIdx.x < 33) {
-        const uint32_t b = threadIdx.x;
-#pragma unroll
-        for (int d = 0; d < 4; ++d) {
-            const uint32_t r = b < 32 ? (((2u << d) - 1u) << b) : 0u;
-            s_init[b][2 * d] = r;
-            s_init[b][2 * d + 1] = r << 1;
-        }
-    }
-    if (lane < 4) s_cnt[warp][lane] = 0ull;
-    __syncthreads();
-    // opaque copies: ptxas otherwise re-derives these shared-memory addresses from SR_CgaCtaId in every loop iteration
-    uint32_t init_a = smem_u32(&s_init[0][0]);
-    asm volatile("mov.u32 %0, %0;" : "+r"(init_a));
-    uint32_t *prefix = s_prefix[warp], *start = s_start[warp], *list = s_list[warp], *tmp = s_tmp[warp];
-    const uint32_t pair_a = smem_u32(&s_pair[warp][0][0]);
-    const uint32_t v_a = smem_u32(&s_v[warp][0]);
-    const unsigned int n_items = GEN ? p.ctr->n_wide : p.ctr->n_fast;
-    unsigned int *cursor = GEN ? &p.ctr->cur_wide : &p.ctr->cur_fast;
-    const int *items = GEN ? p.wide_list : p.fast_list;
-    const int bl = p.bl;
+template <int KP, bool BL16, bool PRE, bool GEN>
+__device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex &ix, const SeedWarp &w, const int lane,
+                                           const int seg, const long long so, const int n_total,
+                                           const unsigned long long *__restrict__ pw, const int bl, int &best, int &count) {
+    constexpr int K = KP;
     const int P = ix.n_pieces;
     const int stride = 32 - bl - K;                                      // GEN: window step (>= 13 for bl <= 16, K <= 3)
     const uint32_t lt_mask = (1u << lane) - 1u;
-
-    for (;;) {
-        unsigned int idx = 0;
-        if (lane == 0) idx = atomicAdd(cursor, 1u);
-        idx = __shfl_sync(FULL, idx, 0);
-        if (idx >= n_items) break;
-        const int seg = items[idx];
-        const long long so = p.seg_off[seg] - p.b0;
-        const int n_total = (int)(p.seg_off[seg + 1] - p.b0 - so);
-        const unsigned long long *pw = p.pk + (so >> 5) + seg;
-        int best = K + 1, count = 0;
-        uint32_t *queue = s_queue[warp];
-        for (int ws = 0;; ws += stride) {                                // windows (exactly one when !GEN)
+    const bool pre_on = PRE && ix.prefilter != 0;
+    uint32_t *prefix = w.prefix, *start = w.start, *list = w.list, *queue = w.queue;
+    const uint32_t pair_a = w.pair_a;
+    best = K + 1;
+    count = 0;
+    for (int ws = 0;; ws += stride) {                                    // windows (exactly one when !GEN)
         int n;
         unsigned long long fw;
         if (!GEN) {
@@ -297,7 +267,7 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
 #pragma unroll
             for (int d = 0; d < 4; ++d) {
                 const uint32_t m = __ballot_sync(FULL, (vb >> d) & 1u);
-                if (lane == d) s_v[warp][d] = m;
+                if (lane == d) w.v[d] = m;
             }
         }
         // reverse complement of the packed text: complement, reverse the 2-bit groups, drop the unused tail
@@ -305,7 +275,8 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
         rc = ((rc & 0x5555555555555555ull) << 1) | ((rc >> 1) & 0x5555555555555555ull);
         rc >>= (64 - 2 * n);
         // Eq masks (bit j+1 of Eq[c] = [T[j] == c]) of both strands, stored as pair tables: lane = strand * 16 + entry
-        {
+        // (a later phase of a one-window segment finds them in place)
+        if (GEN || ix.first_phase) {
             const uint32_t cj = (uint32_t)(fw >> (2 * lane)) & 3u;
             const bool in = lane < n;
             uint32_t bf[4];
@@ -317,7 +288,7 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
                 const uint32_t b = cc == 0 ? bf[0] : cc == 1 ? bf[1] : cc == 2 ? bf[2] : bf[3];
                 return fwd ? (b << 1) : (__brev(b) >> (31 - n));          // ... and reversed positions
             };
-            s_pair[warp][lane >> 4][lane & 15] = make_uint2(eq_of(lane & 3u), eq_of((lane >> 2) & 3u));
+            w.pair[lane] = make_uint2(eq_of(lane & 3u), eq_of((lane >> 2) & 3u));
         }
         // bucket ranges of every (strand, piece, position); the non-empty ones become slots, prefix-summed in order
         uint32_t total = 0;
@@ -358,21 +329,21 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
                         const uint32_t b0 = left ? (uint32_t)(n - lane) : (uint32_t)lane + ((pre >> 9) & 31u);
                         aux |= (2u * (pre & 31u)) | (left << 6) | ((((uint32_t)s) ^ left) << 7) | (b0 << 21);
                     }
-                    s_aux[warp][slot] = aux;
+                    w.aux[slot] = aux;
                 }
                 n_slots += __popc(live);
                 total += __shfl_sync(FULL, incl, 31);
             }
         }
         prefix[n_slots + lane] = 0xFFFFFFFFu;
-        const bool use_map = MAPW > 0 && total <= 32u * MAPW;
+        const bool use_map = total <= 32u * SEED_MAPW;
         if (use_map)
-            for (uint32_t w = lane; w < (total + 31u) / 32u; w += 32) s_map[warp][w] = 0u;
+            for (uint32_t x = lane; x < (total + 31u) / 32u; x += 32) w.map[x] = 0u;
         __syncwarp();
         if (use_map) {
             for (int i = 1 + lane; i < n_slots; i += 32) {
                 const uint32_t t = prefix[i] - 1u;
-                atomicOr(&s_map[warp][t >> 5], 1u << (t & 31u));
+                atomicOr(&w.map[t >> 5], 1u << (t & 31u));
             }
             __syncwarp();
         }
@@ -385,7 +356,7 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
             if (valid) {
                 if (GEN) {
                     const uint2 words = __ldg(ix.ewords + entry);
-                    level = seed_verify<K, BL16, true>(strand ? words.x : words.y, bl, pair_a + 128u, full, ix.two, v_a);
+                    level = seed_verify<K, BL16, true>(strand ? words.x : words.y, bl, pair_a + 128u, full, ix.two, w.v_a);
                 } else {
                     const uint32_t word = __ldg(&ix.ewords[entry].x);
                     level = seed_verify<K, BL16, false>(word, bl, pair_a + strand * 128u, full, ix.two, 0u);
@@ -414,7 +385,7 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
             // slots starting at t0 + r, 1 <= r <= 32, as bit r-1: a lane's slot is cur + #starts at or before it
             uint32_t heads;
             if (use_map) {
-                heads = s_map[warp][t0 >> 5];
+                heads = w.map[t0 >> 5];
             } else {
                 const uint32_t rel = prefix[cur + 1 + lane] - t0 - 1u;
                 heads = __reduce_or_sync(FULL, rel < 32u ? (1u << rel) : 0u);
@@ -425,12 +396,14 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
             // branch-free: the lanes past the end of the last block run the check on whatever follows the last bucket
             // (the entry array is padded by 32 entries) and are masked out
             const uint32_t entry = start[pos] + me;
-            const uint32_t aux = s_aux[warp][pos];
+            const uint32_t aux = w.aux[pos];
             const uint32_t item = entry | ((aux & 256u) << 23);           // strand in bit 31
             bool pass = me < total;
             if (BL16 && PRE) {
-                const uint2 words = __ldg(ix.ewords + entry);
-                pass = seed_precheck<K>(words, aux, pair_a, full, ix.two, init_a) && pass;
+                if (pre_on) {
+                    const uint2 words = __ldg(ix.ewords + entry);
+                    pass = seed_precheck<K>(words, aux, pair_a, full, ix.two, w.init_a) && pass;
+                }
             }
             const unsigned pm = __ballot_sync(FULL, pass);
             if (pass) queue[qn + __popc(pm & lt_mask)] = item;
@@ -450,17 +423,110 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
         if (qn > 0) verify(lane < qn ? queue[lane] : 0u, lane < qn);
         n_ver += (uint32_t)qn;
         if (lane == 0) {
-            s_cnt[warp][0] += n_probe;
-            s_cnt[warp][1] += n_ver;
-            s_cnt[warp][2] += total;
-            s_cnt[warp][3] += 1ull;
+            w.cnt[0] += n_probe;
+            w.cnt[1] += n_ver;
+            w.cnt[2] += total;
+            w.cnt[3] += 1ull;
+            // automaton steps performed (x (2K+1) LOP3 each): full verifications + anchored pre-checks
+            w.cnt[4] += (unsigned long long)((n_ver * (uint32_t)bl + (pre_on ? total * 2u * (uint32_t)seed_pre_pairs(K) : 0u)) *
+                                             (uint32_t)(2 * K + 1));
+            if (pre_on) w.cnt[5] += total;
         }
         __syncwarp();
         if (!GEN || ws + SEED_MAX_LEN >= n_total) break;
+    }
+}
+
+// The seeded match kernel.  One warp per segment; ITERATIVE DEEPENING over the error bound: phase k' looks for every
+// barcode within k' edits with the seeds of k' + 1 pieces (k' = 1: two 8-mers, ~12 candidates per segment at B = 25 k;
+// k' = 2: 5+5+6, ~1 100; k' = 3: four 4-mers, ~9 300) and the search stops at the first phase that finds something: the
+// reference reports only the minimum distance and the barcodes tied at it (scTagger.py:643-668), and phase k' is complete
+// for every distance <= k', so a segment with an exact or one-error hit never pays for the wide search.  ixs.ph[i] is the
+// index of phase i (error bound ixs.first_k + i); with deepening switched off there is one phase, the final bound.
+struct SeedPhases {
+    SeedIndex ph[3];
+    int n_phases;
+};
+
+template <int K, bool BL16, bool PRE, bool GEN>
+__global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(const MatchParams p, const SeedPhases ixs) {
+    constexpr int NSLOT = 2 * (K + 1) * 32;
+    // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
+    __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
+    __shared__ uint32_t s_start[SEED_WARPS][NSLOT];            // first entry of the bucket - index of its first candidate
+    __shared__ uint32_t s_aux[SEED_WARPS][NSLOT];              // strand << 8 | pre-check operands of the slot (see seed_precheck)
+    __shared__ uint32_t s_queue[SEED_WARPS][SEED_QUEUE_CAP];   // pre-check survivors: entry | strand << 31
+    // bit t-1 = "a slot starts at candidate t": word j is the slot-start mask of candidates 32j+1 .. 32j+32.  Used when
+    // the window's candidates fit (always at -mr <= 2 on real data); otherwise the mask is derived from s_prefix.
+    __shared__ uint32_t s_map[SEED_WARPS][SEED_MAPW];
+    __shared__ __align__(128) uint2 s_pair[SEED_WARPS][2][16]; // per strand: entry c0 | c1 << 2 = {Eq[c0], Eq[c1]}
+    __shared__ uint32_t s_list[SEED_WARPS][SEED_LIST_CAP];
+    __shared__ uint32_t s_tmp[SEED_WARPS][SEED_LIST_CAP];
+    __shared__ __align__(16) uint32_t s_init[33][8];           // pre-check start states by boundary: R0 S0 R1 S1 R2 S2 R3 S3
+    __shared__ __align__(16) uint32_t s_v[SEED_WARPS][4];      // GEN: start states of the window per level
+    __shared__ unsigned long long s_cnt[SEED_WARPS][8];        // work counters (see the flush at the end)
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x < 33) {
+        const uint32_t b = threadIdx.x;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            const uint32_t r = b < 32 ? (((2u << d) - 1u) << b) : 0u;
+            s_init[b][2 * d] = r;
+            s_init[b][2 * d + 1] = r << 1;
         }
+    }
+    if (lane < 8) s_cnt[warp][lane] = 0ull;
+    __syncthreads();
+    SeedWarp w;
+    w.prefix = s_prefix[warp];
+    w.start = s_start[warp];
+    w.aux = s_aux[warp];
+    w.queue = s_queue[warp];
+    w.map = s_map[warp];
+    w.list = s_list[warp];
+    w.tmp = s_tmp[warp];
+    w.v = s_v[warp];
+    w.pair = &s_pair[warp][0][0];
+    w.cnt = s_cnt[warp];
+    // opaque copies: ptxas otherwise re-derives these shared-memory addresses from SR_CgaCtaId in every loop iteration
+    w.init_a = smem_u32(&s_init[0][0]);
+    asm volatile("mov.u32 %0, %0;" : "+r"(w.init_a));
+    w.pair_a = smem_u32(&s_pair[warp][0][0]);
+    w.v_a = smem_u32(&s_v[warp][0]);
+    const unsigned int n_items = GEN ? p.ctr->n_wide : p.ctr->n_fast;
+    unsigned int *cursor = GEN ? &p.ctr->cur_wide : &p.ctr->cur_fast;
+    const int *items = GEN ? p.wide_list : p.fast_list;
+    const int bl = p.bl;
+    const int last = ixs.n_phases - 1;
+
+    for (;;) {
+        unsigned int idx = 0;
+        if (lane == 0) idx = atomicAdd(cursor, 1u);
+        idx = __shfl_sync(FULL, idx, 0);
+        if (idx >= n_items) break;
+        const int seg = items[idx];
+        const long long so = p.seg_off[seg] - p.b0;
+        const int n_total = (int)(p.seg_off[seg + 1] - p.b0 - so);
+        const unsigned long long *pw = p.pk + (so >> 5) + seg;
+        int best = K + 1, count = 0;
+        // phase i has error bound K - last + i: the last phase is always the full bound K
+        if constexpr (K >= 3) {
+            if (last >= 2) {
+                seed_phase<K - 2, BL16, PRE, GEN>(p, ixs.ph[last - 2], w, lane, seg, so, n_total, pw, bl, best, count);
+                if (best > K - 2) best = K + 1;
+            }
+        }
+        if constexpr (K >= 2) {
+            if (last >= 1 && best > K) {
+                seed_phase<K - 1, BL16, PRE, GEN>(p, ixs.ph[last - 1], w, lane, seg, so, n_total, pw, bl, best, count);
+                if (best > K - 1) best = K + 1;
+            }
+        }
+        if (best > K) seed_phase<K, BL16, PRE, GEN>(p, ixs.ph[last], w, lane, seg, so, n_total, pw, bl, best, count);
         // more hits than the list holds (in GEN mode possibly only duplicates from overlapping windows): exact re-run
-        if (count <= SEED_LIST_CAP) count = sort_unique(list, tmp, count, lane);
-        store_result(p, seg, lane, K, best, count, list, SEED_LIST_CAP, true);
+        if (count <= SEED_LIST_CAP) count = sort_unique(w.list, w.tmp, count, lane);
+        store_result(p, seg, lane, K, best, count, w.list, SEED_LIST_CAP, true);
         __syncwarp();
     }
     if (lane == 0) {
@@ -468,7 +534,8 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
         if (s_cnt[warp][0]) atomicAdd(&p.ctr->n_probe, s_cnt[warp][0]);
         if (s_cnt[warp][1]) atomicAdd(&p.ctr->n_verify, s_cnt[warp][1]);
         if (s_cnt[warp][3]) atomicAdd(&p.ctr->n_setup, s_cnt[warp][3]);
-        if (PRE && s_cnt[warp][2]) atomicAdd(&p.ctr->n_precheck, s_cnt[warp][2]);
+        if (s_cnt[warp][4]) atomicAdd(&p.ctr->n_lop3, s_cnt[warp][4]);
+        if (s_cnt[warp][5]) atomicAdd(&p.ctr->n_precheck, s_cnt[warp][5]);
     }
 }
 

@@ -229,6 +229,33 @@ def test_full_size_properties():
         assert ((int(pick[i]) << 1) | 1) in r.ties(i).tolist()
 
 
+@pytest.mark.parametrize("mr", [1, 2, 3])
+@pytest.mark.parametrize("deepening,prefilter", [(1, -1), (0, -1), (1, 1), (0, 1), (1, 0)])
+def test_iterative_deepening_and_prefilter_options(mr, deepening, prefilter):
+    """The seeded kernel searches error bounds 1, 2, .. -mr in turn and stops at the first bound with a hit (the
+    reference reports the minimum distance and its ties only).  Every combination of deepening on/off and anchored
+    pre-check auto/forced/off must give the oracle's result, on short, long and dirty segments alike."""
+    rng = np.random.default_rng(7000 + mr)
+    bc, sb, off = util.random_case(rng, 3000, 4000, bl=16, dirty=0.1, lower=True, max_len=31)
+    bc2, sb2, off2 = util.long_case(rng, 3000, 600, bl=16, min_len=20, max_len=90, dirty=0.3)
+    sb = np.concatenate([sb, sb2])
+    off = np.concatenate([off, off[-1] + off2[1:]])
+    want = oracle.match(bc, sb, off, mr, threads=16, algo="dp")
+    with _lib.Matcher(bc, mr, 16, seed_deepening=deepening, seed_prefilter=prefilter) as m:
+        got = m.match(sb, off)
+        wk = m.work_counters()
+    _assert_same(got, want)
+    n_seeded = int(((off[1:] - off[:-1]) >= 16 - mr).sum())
+    if deepening and mr > 1:
+        assert n_seeded < wk["phases_run"]                      # some segments needed a wider bound ...
+    elif not deepening:
+        assert wk["phases_run"] >= n_seeded                      # ... without deepening every window runs one phase
+    if prefilter == 0:
+        assert wk["prechecks"] == 0
+    if prefilter == 1:
+        assert wk["prechecks"] > 0
+
+
 @pytest.mark.parametrize("mr", [2, 3])
 def test_baseline_config_1m_seeded_equals_all_pairs_kernel(mr):
     """BASELINE configs[1] (and configs[3]'s shape per GPU) at FULL size, 1 M segments x 25 k barcodes: the seeded kernel
@@ -244,6 +271,8 @@ def test_baseline_config_1m_seeded_equals_all_pairs_kernel(mr):
         assert m.stats()["seed_candidates"] == 0
     _assert_same(seeded, tiles)
     with _lib.Matcher(bc, mr, 16, seed_prefilter=0) as m:
+        _assert_same(m.match(sb, off), seeded)
+    with _lib.Matcher(bc, mr, 16, seed_deepening=0) as m:     # the full error bound in one phase
         _assert_same(m.match(sb, off), seeded)
     rows = int((seeded.min_ed >= 0).sum())
     assert rows == (887_994 if mr == 2 else 999_977)          # the bench's row counts for this seed
