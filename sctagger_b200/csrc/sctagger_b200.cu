@@ -72,6 +72,7 @@ struct sct_handle {
     SeedIndex seed_by_k[4] = {};  // index of error bound k (k = 0 only when -mr 0), built in sct_create for k = 1..K
     bool seed_pre_by_k[4] = {false, false, false, false};   // the anchored pre-check is possible for this bound
     int seed_deepening = 1;       // option: search error bounds 1, 2, .. K in turn and stop at the first hit
+    int seed_direct_opt = -1;     // option seed_direct: -1 auto (sparse indexes), 0 never, 1 every phase
     int seed_prefilter_opt = -1;  // option seed_prefilter: -1 auto (per phase, by expected bucket size), 0 off, 1 on where possible
     size_t fast_smem = 0;
     int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
@@ -239,6 +240,9 @@ bool seed_phases(const sct_handle *h, SeedPhases &ph) {
         bool on = h->seed_pre_by_k[k] && h->bl == 16;
         if (h->seed_prefilter_opt == 0) on = false;
         else if (h->seed_prefilter_opt < 0) on = on && per_probe >= 2.0;
+        // a sparse index (less than one barcode per bucket) is probed and verified per lane, without slot table / queue
+        ix.direct = (h->seed_direct_opt < 0 ? per_probe < 1.0 : h->seed_direct_opt != 0) ? 1 : 0;
+        if (ix.direct) on = false;
         ix.prefilter = on ? 1 : 0;
         any = any || on;
     }
@@ -684,6 +688,7 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
                 ix.two = 2u;
                 ix.prefilter = 0;
                 ix.first_phase = 0;
+                ix.direct = 0;
             }
             h->seed_pre_ok = h->seed_ok && h->seed_pre_by_k[max_error];
         }
@@ -751,6 +756,8 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "seed_prefilter") {
         if (value > 0 && !h->seed_pre_ok) return fail(SCT_E_ARG, "seed_prefilter is not available for this barcode length / -mr");
         h->seed_prefilter_opt = value < 0 ? -1 : (value != 0 ? 1 : 0);   // -1 auto, 0 off, 1 on wherever possible
+    } else if (k == "seed_direct") {        // -1 auto, 0 slot-table path for every phase, 1 per-lane path for every phase
+        h->seed_direct_opt = value < 0 ? -1 : (value != 0 ? 1 : 0);
     } else if (k == "seed_deepening") {     // 1 (default): error bounds 1..K in turn, stop at the first hit; 0: bound K only
         h->seed_deepening = value != 0 ? 1 : 0;
     } else if (k == "ramp_segments") {

@@ -47,6 +47,7 @@ struct SeedIndex {
     uint32_t pre[SEED_MAX_PIECES];
     int prefilter;                         // 1 = run the anchored pre-check (option "seed_prefilter")
     int first_phase;                       // 1 = this phase builds the segment's Eq tables (the first one that runs)
+    int direct;                            // 1 = sparse index: probe and verify per lane, no slot table (seed_phase_direct)
 };
 __host__ __device__ constexpr int seed_pre_pairs(int K) { return K >= 3 ? 4 : 3; }   // 6 characters; 8 at -mr 3
 constexpr int SEED_QUEUE_CAP = 64;         // pre-check survivors waiting for a full verification, per warp
@@ -219,6 +220,159 @@ struct SeedWarp {
 };
 constexpr int SEED_MAPW = 128;   // slot-start bitmap: candidates 1..4096 of a window
 
+// The text of one window: packed forward text, its reverse complement, (GEN) the start states of the window, and —
+// when asked — the Eq pair tables of both strands in the warp's shared memory.
+template <bool GEN>
+__device__ __forceinline__ void seed_window(const MatchParams &p, const SeedWarp &w, const int lane, const int seg,
+                                            const long long so, const int n_total, const unsigned long long *__restrict__ pw,
+                                            const int ws, const bool build_eq, int &n, unsigned long long &fw,
+                                            unsigned long long &rc) {
+    if (!GEN) {
+        n = n_total;
+        fw = __ldg(pw);
+    } else {
+        n = min(SEED_MAX_LEN, n_total - ws);
+        const unsigned long long a = __ldg(pw + (ws >> 5)), b = __ldg(pw + (ws >> 5) + 1);
+        const int sh = 2 * (ws & 31);
+        fw = sh ? ((a >> sh) | (b << (64 - sh))) : a;
+        fw &= (1ull << (2 * n)) - 1ull;
+        // start states: bit j of level d = [D0[ws + j] <= d], j = 0..n
+        uint32_t vb = 0;
+        if (lane <= n) {
+            const int pos = ws + lane;
+            vb = pos == 0 ? ((p.segflag[seg] & SEG_START0) ? 0xFu : 0u) : (uint32_t)(p.colinfo[so + pos - 1] >> 3);
+        }
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            const uint32_t m = __ballot_sync(FULL, (vb >> d) & 1u);
+            if (lane == d) w.v[d] = m;
+        }
+    }
+    // reverse complement of the packed text: complement, reverse the 2-bit groups, drop the unused tail
+    rc = __brevll(~fw);
+    rc = ((rc & 0x5555555555555555ull) << 1) | ((rc >> 1) & 0x5555555555555555ull);
+    rc >>= (64 - 2 * n);
+    // Eq masks (bit j+1 of Eq[c] = [T[j] == c]) of both strands, stored as pair tables: lane = strand * 16 + entry
+    // (a later phase of a one-window segment finds them in place)
+    if (build_eq) {
+        const uint32_t cj = (uint32_t)(fw >> (2 * lane)) & 3u;
+        const bool in = lane < n;
+        uint32_t bf[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) bf[c] = __ballot_sync(FULL, in && cj == (uint32_t)c);
+        const bool fwd = lane >= 16;                                  // strand 1 = forward text
+        auto eq_of = [&](uint32_t c) -> uint32_t {
+            const uint32_t cc = fwd ? c : 3u - c;                     // reverse strand: complement ...
+            const uint32_t b = cc == 0 ? bf[0] : cc == 1 ? bf[1] : cc == 2 ? bf[2] : bf[3];
+            return fwd ? (b << 1) : (__brev(b) >> (31 - n));          // ... and reversed positions
+        };
+        w.pair[lane] = make_uint2(eq_of(lane & 3u), eq_of((lane >> 2) & 3u));
+    }
+}
+
+// Fold the exact levels of up to 32 candidates (one per lane, K + 1 = no match) into the warp's running (minimum, tie list).
+__device__ __forceinline__ void seed_fold(const int level, const uint32_t entry, const uint32_t strand, const int K,
+                                          const uint32_t *__restrict__ eids, uint32_t *list, const uint32_t lt_mask,
+                                          int &best, int &count) {
+    const unsigned hit = __ballot_sync(FULL, level <= K);
+    if (hit) {
+        const int m = __reduce_min_sync(FULL, level);
+        if (m <= best) {
+            if (m < best) {
+                best = m;
+                count = 0;
+            }
+            const unsigned mine = __ballot_sync(FULL, level == m);
+            if (level == m) {
+                const int at = count + __popc(mine & lt_mask);
+                if (at < SEED_LIST_CAP) list[at] = (__ldg(eids + entry) << 1) | strand;
+            }
+            count += __popc(mine);
+        }
+    }
+}
+
+// A phase whose index is SPARSE (fewer than one barcode per bucket on average: the two 8-mers of error bound 1 at
+// B = 25 k): no slot table, no queue, no pre-check.  Every lane probes one (strand, piece, position) bucket and the warp
+// verifies bucket entry 0 of every lane, then entry 1, ... — one or two rounds of full verifications per window.
+template <int KP, bool BL16, bool GEN>
+__device__ __forceinline__ void seed_phase_direct(const MatchParams &p, const SeedIndex &ix, const SeedWarp &w, const int lane,
+                                                  const int seg, const long long so, const int n_total,
+                                                  const unsigned long long *__restrict__ pw, const int bl, int &best, int &count) {
+    constexpr int K = KP;
+    const int P = ix.n_pieces;
+    const int stride = 32 - bl - K;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    best = K + 1;
+    count = 0;
+    for (int ws = 0;; ws += stride) {
+        int n;
+        unsigned long long fw, rc;
+        seed_window<GEN>(p, w, lane, seg, so, n_total, pw, ws, GEN || ix.first_phase != 0, n, fw, rc);
+        const uint32_t full = (n >= 31) ? 0xFFFFFFFFu : ((1u << (n + 1)) - 1u);
+        int lo[K + 1], cnt[K + 1], per = 0;
+#pragma unroll
+        for (int q = 0; q <= K; ++q) {
+            lo[q] = cnt[q] = 0;
+            if (q < P) {
+                const int o = ix.piece_off[q], ln = ix.piece_len[q];
+                lo[q] = max(0, o - K);
+                cnt[q] = max(0, min(n - ln, n - (bl - o) + K) - lo[q] + 1);
+                per += cnt[q];
+            }
+        }
+        __syncwarp();                                                  // Eq tables / start states visible
+        uint32_t n_ver = 0;
+        for (int c0 = 0; c0 < 2 * per; c0 += 32) {
+            const int c = c0 + lane;
+            const uint32_t strand = c >= per ? 1u : 0u;
+            int r = c - (strand ? per : 0);
+            uint32_t st = 0, en = 0;
+            if (c < 2 * per) {
+                const unsigned long long text = strand ? fw : rc;
+#pragma unroll
+                for (int q = 0; q <= K; ++q) {
+                    if (q < P) {
+                        if (r >= 0 && r < cnt[q]) {
+                            const int j = lo[q] + r;
+                            const uint32_t h = (uint32_t)(text >> (2 * j)) & ((1u << (2 * ix.piece_len[q])) - 1u);
+                            const uint32_t *b = ix.boff + ix.boff_base[q] + h;
+                            st = __ldg(b);
+                            en = __ldg(b + 1);
+                        }
+                        r -= cnt[q];
+                    }
+                }
+            }
+            while (__any_sync(FULL, st < en)) {
+                const bool valid = st < en;
+                int level = K + 1;
+                if (valid) {
+                    if (GEN) {
+                        const uint2 words = __ldg(ix.ewords + st);
+                        level = seed_verify<K, BL16, true>(strand ? words.x : words.y, bl, w.pair_a + 128u, full, ix.two, w.v_a);
+                    } else {
+                        const uint32_t word = __ldg(&ix.ewords[st].x);
+                        level = seed_verify<K, BL16, false>(word, bl, w.pair_a + strand * 128u, full, ix.two, 0u);
+                    }
+                }
+                n_ver += (uint32_t)__popc(__ballot_sync(FULL, valid));
+                seed_fold(level, st, strand, K, ix.eids, w.list, lt_mask, best, count);
+                st += valid ? 1u : 0u;
+            }
+        }
+        if (lane == 0) {
+            w.cnt[0] += (unsigned long long)(2 * per);
+            w.cnt[1] += n_ver;
+            w.cnt[2] += n_ver;
+            w.cnt[3] += 1ull;
+            w.cnt[4] += (unsigned long long)(n_ver * (uint32_t)bl * (uint32_t)(2 * K + 1));
+        }
+        __syncwarp();
+        if (!GEN || ws + SEED_MAX_LEN >= n_total) break;
+    }
+}
+
 // One PHASE of the search for one segment: every (barcode, strand) within KP edits, exactly (pigeonhole seeds of the
 // phase's index -> anchored pre-check -> full verification), folded into (best, count, list).  best = KP + 1 when there
 // is none.
@@ -248,48 +402,8 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
     count = 0;
     for (int ws = 0;; ws += stride) {                                    // windows (exactly one when !GEN)
         int n;
-        unsigned long long fw;
-        if (!GEN) {
-            n = n_total;
-            fw = __ldg(pw);
-        } else {
-            n = min(SEED_MAX_LEN, n_total - ws);
-            const unsigned long long a = __ldg(pw + (ws >> 5)), b = __ldg(pw + (ws >> 5) + 1);
-            const int sh = 2 * (ws & 31);
-            fw = sh ? ((a >> sh) | (b << (64 - sh))) : a;
-            fw &= (1ull << (2 * n)) - 1ull;
-            // start states: bit j of level d = [D0[ws + j] <= d], j = 0..n
-            uint32_t vb = 0;
-            if (lane <= n) {
-                const int pos = ws + lane;
-                vb = pos == 0 ? ((p.segflag[seg] & SEG_START0) ? 0xFu : 0u) : (uint32_t)(p.colinfo[so + pos - 1] >> 3);
-            }
-#pragma unroll
-            for (int d = 0; d < 4; ++d) {
-                const uint32_t m = __ballot_sync(FULL, (vb >> d) & 1u);
-                if (lane == d) w.v[d] = m;
-            }
-        }
-        // reverse complement of the packed text: complement, reverse the 2-bit groups, drop the unused tail
-        unsigned long long rc = __brevll(~fw);
-        rc = ((rc & 0x5555555555555555ull) << 1) | ((rc >> 1) & 0x5555555555555555ull);
-        rc >>= (64 - 2 * n);
-        // Eq masks (bit j+1 of Eq[c] = [T[j] == c]) of both strands, stored as pair tables: lane = strand * 16 + entry
-        // (a later phase of a one-window segment finds them in place)
-        if (GEN || ix.first_phase) {
-            const uint32_t cj = (uint32_t)(fw >> (2 * lane)) & 3u;
-            const bool in = lane < n;
-            uint32_t bf[4];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) bf[c] = __ballot_sync(FULL, in && cj == (uint32_t)c);
-            const bool fwd = lane >= 16;                                  // strand 1 = forward text
-            auto eq_of = [&](uint32_t c) -> uint32_t {
-                const uint32_t cc = fwd ? c : 3u - c;                     // reverse strand: complement ...
-                const uint32_t b = cc == 0 ? bf[0] : cc == 1 ? bf[1] : cc == 2 ? bf[2] : bf[3];
-                return fwd ? (b << 1) : (__brev(b) >> (31 - n));          // ... and reversed positions
-            };
-            w.pair[lane] = make_uint2(eq_of(lane & 3u), eq_of((lane >> 2) & 3u));
-        }
+        unsigned long long fw, rc;
+        seed_window<GEN>(p, w, lane, seg, so, n_total, pw, ws, GEN || ix.first_phase != 0, n, fw, rc);
         // bucket ranges of every (strand, piece, position); the non-empty ones become slots, prefix-summed in order
         uint32_t total = 0;
         int n_slots = 0;
@@ -362,22 +476,7 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
                     level = seed_verify<K, BL16, false>(word, bl, pair_a + strand * 128u, full, ix.two, 0u);
                 }
             }
-            const unsigned hit = __ballot_sync(FULL, level <= K);
-            if (hit) {
-                const int m = __reduce_min_sync(FULL, level);
-                if (m <= best) {
-                    if (m < best) {
-                        best = m;
-                        count = 0;
-                    }
-                    const unsigned mine = __ballot_sync(FULL, level == m);
-                    if (level == m) {
-                        const int at = count + __popc(mine & lt_mask);
-                        if (at < SEED_LIST_CAP) list[at] = (__ldg(ix.eids + entry) << 1) | strand;
-                    }
-                    count += __popc(mine);
-                }
-            }
+            seed_fold(level, entry, strand, K, ix.eids, list, lt_mask, best, count);
         };
         int qn = 0;
         int cur = 0;                                                    // slot holding candidate t0 (warp-uniform)
@@ -513,17 +612,22 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
         // phase i has error bound K - last + i: the last phase is always the full bound K
         if constexpr (K >= 3) {
             if (last >= 2) {
-                seed_phase<K - 2, BL16, PRE, GEN>(p, ixs.ph[last - 2], w, lane, seg, so, n_total, pw, bl, best, count);
+                if (ixs.ph[last - 2].direct) seed_phase_direct<K - 2, BL16, GEN>(p, ixs.ph[last - 2], w, lane, seg, so, n_total, pw, bl, best, count);
+                else seed_phase<K - 2, BL16, PRE, GEN>(p, ixs.ph[last - 2], w, lane, seg, so, n_total, pw, bl, best, count);
                 if (best > K - 2) best = K + 1;
             }
         }
         if constexpr (K >= 2) {
             if (last >= 1 && best > K) {
-                seed_phase<K - 1, BL16, PRE, GEN>(p, ixs.ph[last - 1], w, lane, seg, so, n_total, pw, bl, best, count);
+                if (ixs.ph[last - 1].direct) seed_phase_direct<K - 1, BL16, GEN>(p, ixs.ph[last - 1], w, lane, seg, so, n_total, pw, bl, best, count);
+                else seed_phase<K - 1, BL16, PRE, GEN>(p, ixs.ph[last - 1], w, lane, seg, so, n_total, pw, bl, best, count);
                 if (best > K - 1) best = K + 1;
             }
         }
-        if (best > K) seed_phase<K, BL16, PRE, GEN>(p, ixs.ph[last], w, lane, seg, so, n_total, pw, bl, best, count);
+        if (best > K) {
+            if (ixs.ph[last].direct) seed_phase_direct<K, BL16, GEN>(p, ixs.ph[last], w, lane, seg, so, n_total, pw, bl, best, count);
+            else seed_phase<K, BL16, PRE, GEN>(p, ixs.ph[last], w, lane, seg, so, n_total, pw, bl, best, count);
+        }
         // more hits than the list holds (in GEN mode possibly only duplicates from overlapping windows): exact re-run
         if (count <= SEED_LIST_CAP) count = sort_unique(w.list, w.tmp, count, lane);
         store_result(p, seg, lane, K, best, count, w.list, SEED_LIST_CAP, true);

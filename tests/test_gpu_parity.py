@@ -230,8 +230,9 @@ def test_full_size_properties():
 
 
 @pytest.mark.parametrize("mr", [1, 2, 3])
-@pytest.mark.parametrize("deepening,prefilter", [(1, -1), (0, -1), (1, 1), (0, 1), (1, 0)])
-def test_iterative_deepening_and_prefilter_options(mr, deepening, prefilter):
+@pytest.mark.parametrize("deepening,prefilter,direct", [(1, -1, -1), (0, -1, -1), (1, 1, 0), (0, 1, 0), (1, 0, 0), (1, -1, 1),
+                                                        (0, -1, 1)])
+def test_iterative_deepening_and_prefilter_options(mr, deepening, prefilter, direct):
     """The seeded kernel searches error bounds 1, 2, .. -mr in turn and stops at the first bound with a hit (the
     reference reports the minimum distance and its ties only).  Every combination of deepening on/off and anchored
     pre-check auto/forced/off must give the oracle's result, on short, long and dirty segments alike."""
@@ -241,7 +242,7 @@ def test_iterative_deepening_and_prefilter_options(mr, deepening, prefilter):
     sb = np.concatenate([sb, sb2])
     off = np.concatenate([off, off[-1] + off2[1:]])
     want = oracle.match(bc, sb, off, mr, threads=16, algo="dp")
-    with _lib.Matcher(bc, mr, 16, seed_deepening=deepening, seed_prefilter=prefilter) as m:
+    with _lib.Matcher(bc, mr, 16, seed_deepening=deepening, seed_prefilter=prefilter, seed_direct=direct) as m:
         got = m.match(sb, off)
         wk = m.work_counters()
     _assert_same(got, want)
@@ -252,8 +253,10 @@ def test_iterative_deepening_and_prefilter_options(mr, deepening, prefilter):
         assert wk["phases_run"] >= n_seeded                      # ... without deepening every window runs one phase
     if prefilter == 0:
         assert wk["prechecks"] == 0
-    if prefilter == 1:
+    if prefilter == 1 and direct == 0:
         assert wk["prechecks"] > 0
+    if direct == 1:                                              # per-lane probe + verify in every phase: no pre-check at all
+        assert wk["prechecks"] == 0
 
 
 @pytest.mark.parametrize("mr", [2, 3])
