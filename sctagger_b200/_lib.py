@@ -12,7 +12,7 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libsctagger_b200.so")
+SO_PATH = os.environ.get("SCT_LIBRARY") or os.path.join(_HERE, "libsctagger_b200.so")   # SCT_LIBRARY: a build variant (tuning)
 
 # every symbol include/sctagger_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = (

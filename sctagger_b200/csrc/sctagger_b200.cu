@@ -228,10 +228,11 @@ MatchParams make_params(sct_handle *h, Slot &s) {
 bool seed_phases(const sct_handle *h, SeedPhases &ph) {
     const int K = h->K;
     const int first = (h->seed_deepening && K >= 1) ? 1 : K;
-    ph.n_phases = K - first + 1;
+    ph.run_mask = 0;
     bool any = false;
     for (int k = first; k <= K; ++k) {
-        SeedIndex &ix = ph.ph[k - first];
+        ph.run_mask |= 1 << k;
+        SeedIndex &ix = ph.ph[k];
         ix = h->seed_by_k[k];
         ix.first_phase = k == first ? 1 : 0;
         int min_len = 99;
@@ -255,7 +256,7 @@ int launch_match(sct_handle *h, Slot &s, const MatchParams &p, int fast /* 0 non
     if (fast == 2) {
         // seeded kernel: small static shared memory, many resident warps (latency-bound gathers + verification)
         const int grid = h->sm_count * h->seed_ctas_per_sm;
-        SeedPhases ph;
+        SeedPhases ph{};
         const bool any_pre = seed_phases(h, ph);
         if (h->bl == 16 && any_pre) match_seed_kernel<K, true, true, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, ph);
         else if (h->bl == 16) match_seed_kernel<K, true, false, false><<<grid, SEED_THREADS, 0, s.stream>>>(p, ph);

@@ -26,6 +26,9 @@
 
 namespace sct {
 
+#ifndef SEED_MIN_CTAS
+#define SEED_MIN_CTAS 5                    // resident CTAs per SM the hot variant is compiled for (48 registers)
+#endif
 constexpr int SEED_THREADS = 256;
 constexpr int SEED_WARPS = SEED_THREADS / 32;
 constexpr int SEED_LIST_CAP = 96;          // hits staged per warp before sort + unique
@@ -216,7 +219,7 @@ struct SeedWarp {
     uint32_t *prefix, *start, *aux, *queue, *map, *list, *tmp, *v;
     uint2 *pair;                 // [2][16]
     unsigned long long *cnt;     // work counters of the warp
-    uint32_t pair_a, v_a, init_a;
+    uint32_t pair_a, v_a, init_a, queue_a;
 };
 constexpr int SEED_MAPW = 128;   // slot-start bitmap: candidates 1..4096 of a window
 
@@ -396,7 +399,14 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
     const int stride = 32 - bl - K;                                      // GEN: window step (>= 13 for bl <= 16, K <= 3)
     const uint32_t lt_mask = (1u << lane) - 1u;
     const bool pre_on = PRE && ix.prefilter != 0;
-    uint32_t *prefix = w.prefix, *start = w.start, *list = w.list, *queue = w.queue;
+    uint32_t *prefix = w.prefix, *start = w.start, *list = w.list;
+    const uint32_t queue_a = w.queue_a;
+    auto q_st = [&](int i, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(queue_a + 4u * (uint32_t)i), "r"(v) : "memory"); };
+    auto q_ld = [&](int i) -> uint32_t {
+        uint32_t v;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(queue_a + 4u * (uint32_t)i) : "memory");
+        return v;
+    };
     const uint32_t pair_a = w.pair_a;
     best = K + 1;
     count = 0;
@@ -505,21 +515,21 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
                 }
             }
             const unsigned pm = __ballot_sync(FULL, pass);
-            if (pass) queue[qn + __popc(pm & lt_mask)] = item;
+            if (pass) q_st(qn + __popc(pm & lt_mask), item);
             qn += __popc(pm);
             if (qn >= 32) {
                 __syncwarp();
-                verify(queue[lane], true);
-                const uint32_t rest = (32 + lane < qn) ? queue[32 + lane] : 0u;
+                verify(q_ld(lane), true);
+                const uint32_t rest = (32 + lane < qn) ? q_ld(32 + lane) : 0u;
                 __syncwarp();
-                queue[lane] = rest;
+                q_st(lane, rest);
                 qn -= 32;
                 n_ver += 32u;
                 __syncwarp();
             }
         }
         __syncwarp();
-        if (qn > 0) verify(lane < qn ? queue[lane] : 0u, lane < qn);
+        if (qn > 0) verify(lane < qn ? q_ld(lane) : 0u, lane < qn);
         n_ver += (uint32_t)qn;
         if (lane == 0) {
             w.cnt[0] += n_probe;
@@ -540,15 +550,15 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
 // barcode within k' edits with the seeds of k' + 1 pieces (k' = 1: two 8-mers, ~12 candidates per segment at B = 25 k;
 // k' = 2: 5+5+6, ~1 100; k' = 3: four 4-mers, ~9 300) and the search stops at the first phase that finds something: the
 // reference reports only the minimum distance and the barcodes tied at it (scTagger.py:643-668), and phase k' is complete
-// for every distance <= k', so a segment with an exact or one-error hit never pays for the wide search.  ixs.ph[i] is the
-// index of phase i (error bound ixs.first_k + i); with deepening switched off there is one phase, the final bound.
+// for every distance <= k', so a segment with an exact or one-error hit never pays for the wide search.  ixs.ph[k] is the
+// index of error bound k; with deepening switched off only the final bound runs.
 struct SeedPhases {
-    SeedIndex ph[3];
-    int n_phases;
+    SeedIndex ph[4];       // indexed by the error bound (statically, so that every field is a fixed constant-bank offset)
+    int run_mask;          // bit k = bound k is searched (the final bound K always is)
 };
 
 template <int K, bool BL16, bool PRE, bool GEN>
-__global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(const MatchParams p, const SeedPhases ixs) {
+__global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : SEED_MIN_CTAS) match_seed_kernel(const MatchParams p, const SeedPhases ixs) {
     constexpr int NSLOT = 2 * (K + 1) * 32;
     // non-empty slots only, in (strand, piece, position) order; 32 sentinels behind the last one
     __shared__ uint32_t s_prefix[SEED_WARPS][NSLOT + 32];
@@ -593,11 +603,12 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
     asm volatile("mov.u32 %0, %0;" : "+r"(w.init_a));
     w.pair_a = smem_u32(&s_pair[warp][0][0]);
     w.v_a = smem_u32(&s_v[warp][0]);
+    w.queue_a = smem_u32(&s_queue[warp][0]);
+    asm volatile("mov.u32 %0, %0;" : "+r"(w.queue_a));
     const unsigned int n_items = GEN ? p.ctr->n_wide : p.ctr->n_fast;
     unsigned int *cursor = GEN ? &p.ctr->cur_wide : &p.ctr->cur_fast;
     const int *items = GEN ? p.wide_list : p.fast_list;
     const int bl = p.bl;
-    const int last = ixs.n_phases - 1;
 
     for (;;) {
         unsigned int idx = 0;
@@ -609,24 +620,23 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : 5) match_seed_kernel(c
         const int n_total = (int)(p.seg_off[seg + 1] - p.b0 - so);
         const unsigned long long *pw = p.pk + (so >> 5) + seg;
         int best = K + 1, count = 0;
-        // phase i has error bound K - last + i: the last phase is always the full bound K
         if constexpr (K >= 3) {
-            if (last >= 2) {
-                if (ixs.ph[last - 2].direct) seed_phase_direct<K - 2, BL16, GEN>(p, ixs.ph[last - 2], w, lane, seg, so, n_total, pw, bl, best, count);
-                else seed_phase<K - 2, BL16, PRE, GEN>(p, ixs.ph[last - 2], w, lane, seg, so, n_total, pw, bl, best, count);
+            if (ixs.run_mask & (1 << (K - 2))) {
+                if (ixs.ph[K - 2].direct) seed_phase_direct<K - 2, BL16, GEN>(p, ixs.ph[K - 2], w, lane, seg, so, n_total, pw, bl, best, count);
+                else seed_phase<K - 2, BL16, PRE, GEN>(p, ixs.ph[K - 2], w, lane, seg, so, n_total, pw, bl, best, count);
                 if (best > K - 2) best = K + 1;
             }
         }
         if constexpr (K >= 2) {
-            if (last >= 1 && best > K) {
-                if (ixs.ph[last - 1].direct) seed_phase_direct<K - 1, BL16, GEN>(p, ixs.ph[last - 1], w, lane, seg, so, n_total, pw, bl, best, count);
-                else seed_phase<K - 1, BL16, PRE, GEN>(p, ixs.ph[last - 1], w, lane, seg, so, n_total, pw, bl, best, count);
+            if ((ixs.run_mask & (1 << (K - 1))) && best > K) {
+                if (ixs.ph[K - 1].direct) seed_phase_direct<K - 1, BL16, GEN>(p, ixs.ph[K - 1], w, lane, seg, so, n_total, pw, bl, best, count);
+                else seed_phase<K - 1, BL16, PRE, GEN>(p, ixs.ph[K - 1], w, lane, seg, so, n_total, pw, bl, best, count);
                 if (best > K - 1) best = K + 1;
             }
         }
         if (best > K) {
-            if (ixs.ph[last].direct) seed_phase_direct<K, BL16, GEN>(p, ixs.ph[last], w, lane, seg, so, n_total, pw, bl, best, count);
-            else seed_phase<K, BL16, PRE, GEN>(p, ixs.ph[last], w, lane, seg, so, n_total, pw, bl, best, count);
+            if (ixs.ph[K].direct) seed_phase_direct<K, BL16, GEN>(p, ixs.ph[K], w, lane, seg, so, n_total, pw, bl, best, count);
+            else seed_phase<K, BL16, PRE, GEN>(p, ixs.ph[K], w, lane, seg, so, n_total, pw, bl, best, count);
         }
         // more hits than the list holds (in GEN mode possibly only duplicates from overlapping windows): exact re-run
         if (count <= SEED_LIST_CAP) count = sort_unique(w.list, w.tmp, count, lane);
