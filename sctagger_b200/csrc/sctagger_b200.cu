@@ -646,19 +646,31 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
                     h->seed_ok = false;
                     break;
                 }
-                // anchored pre-check (seed_precheck): per piece the side of the barcode with more characters left
-                bool pre_ok = true;
-                for (int q = 0; q < P; ++q) {
+                // anchored pre-check (seed_precheck): which side of the piece is tested, and how, follows the responsible-seed
+                // rule of the error bound (bl = 16 only: pieces 8+8 / 5+5+6 / 4+4+4+4)
+                bool pre_ok = bl == 16 && k >= 1 && k <= 3;
+                for (int q = 0; q < P && pre_ok; ++q) {
                     const int po = ix.piece_off[q], ln = ix.piece_len[q];
-                    const int right = bl - (po + ln), left = po;
-                    const bool go_left = left > right;
-                    const int avail = go_left ? left : right;
-                    const int pairs = seed_pre_pairs(k);
-                    if (avail < 2 * pairs) pre_ok = false;
-                    ix.pre[q] = (uint32_t)(go_left ? bl - po : po + ln) | ((go_left ? 1u : 0u) << 5) |
-                                ((uint32_t)pairs << 6) | ((uint32_t)ln << 9);
+                    bool go_left;
+                    int need;                       // characters the test reads on that side
+                    uint32_t lvl1_after5 = 0;
+                    if (k == 1) {                   // sibling half within 1 edit: 6 of its characters
+                        go_left = q == 1;
+                        need = 6;
+                    } else if (k == 2) {            // priority piece 2 > piece 1 > piece 0
+                        go_left = q >= 1;
+                        need = q == 2 ? 6 : 5;
+                        lvl1_after5 = q == 2 ? 0u : 1u;
+                    } else {                        // sibling piece within 1 edit
+                        go_left = (q & 1) != 0;
+                        need = 4;
+                    }
+                    const int avail = go_left ? po : bl - (po + ln);
+                    if (avail < need) pre_ok = false;
+                    ix.pre[q] = (uint32_t)(go_left ? bl - po : po + ln) | ((go_left ? 1u : 0u) << 5) | ((uint32_t)ln << 9) |
+                                (lvl1_after5 << 14);
                 }
-                h->seed_pre_by_k[k] = bl == 16 && pre_ok;
+                h->seed_pre_by_k[k] = pre_ok;
                 std::vector<uint32_t> boff(boff_words, 0u), ei((size_t)P * B);
                 std::vector<uint2> ew((size_t)P * B + 32, make_uint2(0u, 0u));   // + 32: the kernel's branch-free tail reads past the last bucket
                 for (int q = 0; q < P; ++q) {

@@ -46,13 +46,12 @@ struct SeedIndex {
     int boff_base[SEED_MAX_PIECES];        // start of the piece's bucket table inside boff
     uint32_t two;                          // always 2 (run-time so that x*2 stays an FMA-pipe IMAD)
     // anchored pre-check per piece: bits 0-4 = characters to skip (right: piece end; left: bl - piece offset),
-    // bit 5 = extend to the left of the seed, bits 6-8 = pair lookups (0 = no pre-check), bits 9-13 = piece length
+    // bit 5 = extend to the left of the seed, bits 9-13 = piece length, bit 14 = test level 1 after 5 characters
     uint32_t pre[SEED_MAX_PIECES];
     int prefilter;                         // 1 = run the anchored pre-check (option "seed_prefilter")
     int first_phase;                       // 1 = this phase builds the segment's Eq tables (the first one that runs)
     int direct;                            // 1 = sparse index: probe and verify per lane, no slot table (seed_phase_direct)
 };
-__host__ __device__ constexpr int seed_pre_pairs(int K) { return K >= 3 ? 4 : 3; }   // 6 characters; 8 at -mr 3
 constexpr int SEED_QUEUE_CAP = 64;         // pre-check survivors waiting for a full verification, per warp
 
 __device__ __forceinline__ uint32_t mul_rt(uint32_t x, uint32_t m) {
@@ -133,25 +132,39 @@ __device__ __forceinline__ int seed_verify(uint32_t word, int bl, uint32_t tab_a
 }
 
 // Anchored pre-check of one candidate: the seed piece matched the text exactly at position j, so a barcode within K edits
-// THROUGH this seed has the characters next to the piece within K edits of the text next to the match.  The same
-// automaton runs for 2 x pairs characters from the seed boundary outwards, started at the boundary only (bits b0..b0+d
-// at level d: d leading text insertions).  Extending to the left is extending the other strand's text to the right with
+// THROUGH this seed has the characters next to the piece within few edits of the text next to the match.  The same
+// automaton runs for a few characters from the seed boundary outwards, started at the boundary only (bits b0..b0+d at
+// level d: d leading text insertions).  Extending to the left is extending the other strand's text to the right with
 // the reverse complement of the barcode, so both directions use the same pair tables.  A candidate that fails cannot be
-// the surviving piece of any alignment with <= K edits; a barcode within K edits is always reached through one of its
-// surviving pieces (pigeonhole), and that candidate passes.  Measured at -mr 2: 89.8 % of the candidates stop here, at
-// ~100 of the loop's 175 instructions per 32 candidates (a full verification is ~175 more).
+// the RESPONSIBLE seed of any alignment within K edits, and every barcode within K edits has a responsible seed that
+// passes — which seed that is, and what it may assume about its neighbours, depends on the error bound (bl = 16):
+//   K = 1, pieces 8+8:      the exact piece's sibling has <= 1 error: 6 characters of it, levels 0..1.
+//   K = 2, pieces 5+5+6:    responsible = the first exact piece in the order (piece 2, piece 1, piece 0).  Piece 2 (the
+//                           6-mer, fewest candidates) may assume nothing: 6 characters to its left within 2 edits.  Piece
+//                           1 is responsible only if piece 2 has an error, so piece 0 — the 5 characters to its left — has
+//                           <= 1.  Piece 0 is responsible only if pieces 1 and 2 both have exactly one error: the 5
+//                           characters to its right within 1 edit.  One automaton (levels 0..2, 6 steps) serves all three:
+//                           level 1 is sampled after the fifth character and a per-slot flag picks the test.
+//   K = 3, pieces 4+4+4+4:  of the two halves one has <= 1 error, and in it one piece is exact and its sibling has <= 1:
+//                           responsible = that piece; test = its sibling's 4 characters within 1 edit (levels 0..1, 4 steps).
+// Measured at -mr 2 with the 6-character / 2-edit test on every slot: 89.8 % of the candidates stop here.
+__host__ __device__ constexpr int seed_pre_steps(int K) { return K >= 3 ? 4 : 6; }
+__host__ __device__ constexpr int seed_pre_levels(int K) { return K == 2 ? 2 : 1; }   // highest level computed
 template <int K>
 // aux (per slot, built once per segment): bits 0-5 = right shift of the barcode word, bit 6 = extend left (use the
-// reverse-complemented word), bit 7 = which strand's pair table, bits 16-31 = byte offset of the start states (32 * b0)
+// reverse-complemented word), bit 7 = which strand's pair table, bit 9 = (K = 2) test level 1 after 5 characters,
+// bits 16-31 = byte offset of the start states (32 * b0)
 __device__ __forceinline__ bool seed_precheck(uint2 words, uint32_t aux, uint32_t pair_a, uint32_t full, uint32_t two,
                                               uint32_t init_a) {
+    constexpr int LV = seed_pre_levels(K);
+    constexpr int STEPS = seed_pre_steps(K);
     const uint32_t w = ((aux & 64u) ? words.y : words.x) >> (aux & 63u);
     const uint32_t tab_a = pair_a + (aux & 128u);
     const uint32_t st_a = init_a + (aux >> 16);
     // start state of level d = bits b0 .. b0+d, from a per-CTA table indexed by b0: {R0, S0, R1, S1}, {R2, S2, R3, S3}
     uint32_t R[4], S[4];
     asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(S[0]), "=r"(R[1]), "=r"(S[1]) : "r"(st_a));
-    if (K >= 2)
+    if (LV >= 2)
         asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[2]), "=r"(S[2]), "=r"(R[3]), "=r"(S[3]) : "r"(st_a + 16u));
     auto row = [&](uint32_t eq) {
         uint32_t r = S[0] & eq;
@@ -160,7 +173,7 @@ __device__ __forceinline__ bool seed_precheck(uint2 words, uint32_t aux, uint32_
         R[0] = r;
         S[0] = s;
 #pragma unroll
-        for (int d = 1; d <= K; ++d) {
+        for (int d = 1; d <= LV; ++d) {
             const uint32_t t = pR | pS | nS;
             r = (S[d] & eq) | t;
             s = mul_rt(r, two);
@@ -171,17 +184,18 @@ __device__ __forceinline__ bool seed_precheck(uint2 words, uint32_t aux, uint32_
             S[d] = s;
         }
     };
-    // SEED_PRE_PAIRS(K) pair lookups for every piece: sct_create switches the pre-check off when a piece has fewer
-    // characters beside it
+    uint32_t r1_at5 = 0u;
 #pragma unroll
-    for (int m = 0; m < seed_pre_pairs(K); ++m) {
+    for (int m = 0; m < STEPS / 2; ++m) {
         const uint32_t sh = m == 0 ? (w << 3) : (w >> (4 * m - 3));
         uint32_t e0, e1;
         asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(e0), "=r"(e1) : "r"(and_or(sh, 0x78u, tab_a)));
         row(e0);
+        if (K == 2 && m == 2) r1_at5 = R[1];
         row(e1);
     }
-    return (R[K] & full) != 0u;
+    if (K == 2) return (((aux & 512u) ? r1_at5 : R[2]) & full) != 0u;
+    return (R[1] & full) != 0u;
 }
 
 // Sort the warp's hit list ascending and drop duplicates (rank sort through a second buffer).  Returns the new count.
@@ -451,7 +465,7 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
                     if (PRE) {
                         const uint32_t pre = ix.pre[q], left = (pre >> 5) & 1u;
                         const uint32_t b0 = left ? (uint32_t)(n - lane) : (uint32_t)lane + ((pre >> 9) & 31u);
-                        aux |= (2u * (pre & 31u)) | (left << 6) | ((((uint32_t)s) ^ left) << 7) | (b0 << 21);
+                        aux |= (2u * (pre & 31u)) | (left << 6) | ((((uint32_t)s) ^ left) << 7) | (((pre >> 14) & 1u) << 9) | (b0 << 21);
                     }
                     w.aux[slot] = aux;
                 }
@@ -537,8 +551,8 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
             w.cnt[2] += total;
             w.cnt[3] += 1ull;
             // automaton steps performed (x (2K+1) LOP3 each): full verifications + anchored pre-checks
-            w.cnt[4] += (unsigned long long)((n_ver * (uint32_t)bl + (pre_on ? total * 2u * (uint32_t)seed_pre_pairs(K) : 0u)) *
-                                             (uint32_t)(2 * K + 1));
+            w.cnt[4] += (unsigned long long)((n_ver * (uint32_t)bl + 0u) * (uint32_t)(2 * K + 1)) +
+                        (pre_on ? (unsigned long long)total * (uint32_t)(seed_pre_steps(K) * (2 * seed_pre_levels(K) + 1)) : 0ull);
             if (pre_on) w.cnt[5] += total;
         }
         __syncwarp();
