@@ -116,6 +116,9 @@ int free_slot(Slot &s) {
     return SCT_OK;
 }
 
+// Every warp of the seeded kernels may leave the tail of one chunk of the tie buffer unused (seed_store_result).
+unsigned long long seed_tie_slack(const sct_handle *h);
+
 int alloc_ties(Slot &s, unsigned long long cap) {
     dev_free(s.d_tiebuf);
     dev_free(s.d_tieout);
@@ -167,7 +170,7 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         CUDA_TRY(cudaMalloc(&s.d_toff, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_bsums, ((c + SCAN_BLOCK - 1) / SCAN_BLOCK + 1) * sizeof(long long)));
         s.cap_segs = c;
-        const unsigned long long want = (unsigned long long)c * h->tie_per_seg + 4096;
+        const unsigned long long want = (unsigned long long)c * h->tie_per_seg + 4096 + seed_tie_slack(h);
         if (want > s.tie_cap) TRY(alloc_ties(s, want));
     }
     if (bytes > s.cap_bytes) {
@@ -190,6 +193,10 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
         s.pk_words = pkw;
     }
     return SCT_OK;
+}
+
+unsigned long long seed_tie_slack(const sct_handle *h) {
+    return (unsigned long long)h->sm_count * (unsigned long long)(std::max(h->seed_ctas_per_sm, 4) * SEED_WARPS * SEED_TIE_CHUNK) * 2ull;
 }
 
 MatchParams make_params(sct_handle *h, Slot &s) {
@@ -405,7 +412,7 @@ int complete_pass(sct_handle *h, Slot &s) {
             s.redo = false;
             return SCT_OK;
         }
-        const unsigned long long need = s.h_ctr->tie_cursor + 4096;
+        const unsigned long long need = s.h_ctr->tie_cursor + 4096 + seed_tie_slack(h);
         TRY(alloc_ties(s, need));
         s.redo = true;
         TRY(enqueue_pass(h, s, s.n));

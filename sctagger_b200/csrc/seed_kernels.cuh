@@ -26,6 +26,9 @@
 
 namespace sct {
 
+#ifndef SEED_ANCHOR
+#define SEED_ANCHOR 1
+#endif
 #ifndef SEED_MIN_CTAS
 #define SEED_MIN_CTAS 5                    // resident CTAs per SM the hot variant is compiled for (48 registers)
 #endif
@@ -52,6 +55,13 @@ struct SeedIndex {
     int first_phase;                       // 1 = this phase builds the segment's Eq tables (the first one that runs)
     int direct;                            // 1 = sparse index: probe and verify per lane, no slot table (seed_phase_direct)
 };
+#ifndef SEED_BATCH_N
+#define SEED_BATCH_N 4
+#endif
+#ifndef SEED_TIE_CHUNK_N
+#define SEED_TIE_CHUNK_N 64
+#endif
+constexpr int SEED_BATCH = SEED_BATCH_N;   // segments a warp takes per visit of the work cursor
 constexpr int SEED_QUEUE_CAP = 64;         // pre-check survivors waiting for a full verification, per warp
 
 __device__ __forceinline__ uint32_t mul_rt(uint32_t x, uint32_t m) {
@@ -242,11 +252,11 @@ constexpr int SEED_MAPW = 128;   // slot-start bitmap: candidates 1..4096 of a w
 template <bool GEN>
 __device__ __forceinline__ void seed_window(const MatchParams &p, const SeedWarp &w, const int lane, const int seg,
                                             const long long so, const int n_total, const unsigned long long *__restrict__ pw,
-                                            const int ws, const bool build_eq, int &n, unsigned long long &fw,
-                                            unsigned long long &rc) {
+                                            const int ws, const bool build_eq, const unsigned long long fw0, int &n,
+                                            unsigned long long &fw, unsigned long long &rc) {
     if (!GEN) {
         n = n_total;
-        fw = __ldg(pw);
+        fw = fw0;                                                     // fetched with the batch
     } else {
         n = min(SEED_MAX_LEN, n_total - ws);
         const unsigned long long a = __ldg(pw + (ws >> 5)), b = __ldg(pw + (ws >> 5) + 1);
@@ -309,14 +319,50 @@ __device__ __forceinline__ void seed_fold(const int level, const uint32_t entry,
     }
 }
 
+// Exact level (0, 1, or 2 = none) of one candidate of the error-bound-1 phase (pieces 8+8, bl = 16, clean one-window
+// segment), ANCHORED at its seed: the piece matched the text exactly, so within one edit through this seed means that
+// the other half — 8 characters outwards from the seed boundary, same automaton and start states as seed_precheck — costs
+// 0 or 1.  A barcode within one edit has an exact half in its optimal alignment and is found through that seed with its
+// true distance; through any other seed occurrence it can only score the same or worse, and the fold keeps the minimum.
+// Half the steps of a full verification, and two levels.
+__device__ __forceinline__ int seed_anchor_level1(uint2 words, uint32_t aux, uint32_t pair_a, uint32_t full, uint32_t two,
+                                                  uint32_t init_a) {
+    const uint32_t w = ((aux & 64u) ? words.y : words.x) >> (aux & 63u);
+    const uint32_t tab_a = pair_a + (aux & 128u);
+    uint32_t R0, S0, R1, S1;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R0), "=r"(S0), "=r"(R1), "=r"(S1) : "r"(init_a + (aux >> 16)));
+    auto row = [&](uint32_t eq) {
+        const uint32_t r0 = S0 & eq;
+        const uint32_t s0 = mul_rt(r0, two);
+        const uint32_t t = R0 | S0 | s0;
+        const uint32_t r1 = (S1 & eq) | t;
+        R0 = r0;
+        S0 = s0;
+        R1 = r1;
+        S1 = mul_rt(r1, two);
+    };
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+        const uint32_t sh = m == 0 ? (w << 3) : (w >> (4 * m - 3));
+        uint32_t e0, e1;
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(e0), "=r"(e1) : "r"(and_or(sh, 0x78u, tab_a)));
+        row(e0);
+        row(e1);
+    }
+    return (R0 & full) ? 0 : ((R1 & full) ? 1 : 2);
+}
+
 // A phase whose index is SPARSE (fewer than one barcode per bucket on average: the two 8-mers of error bound 1 at
 // B = 25 k): no slot table, no queue, no pre-check.  Every lane probes one (strand, piece, position) bucket and the warp
-// verifies bucket entry 0 of every lane, then entry 1, ... — one or two rounds of full verifications per window.
+// verifies bucket entry 0 of every lane, then entry 1, ... — one or two rounds per window.  Error bound 1 on a clean
+// one-window segment verifies anchored at the seed (8 steps, 2 levels) instead of over the whole barcode.
 template <int KP, bool BL16, bool GEN>
 __device__ __forceinline__ void seed_phase_direct(const MatchParams &p, const SeedIndex &ix, const SeedWarp &w, const int lane,
                                                   const int seg, const long long so, const int n_total,
-                                                  const unsigned long long *__restrict__ pw, const int bl, int &best, int &count) {
+                                                  const unsigned long long *__restrict__ pw, const unsigned long long fw0, const int bl,
+        int &best, int &count) {
     constexpr int K = KP;
+    constexpr bool ANCH = SEED_ANCHOR && BL16 && !GEN && KP == 1;
     const int P = ix.n_pieces;
     const int stride = 32 - bl - K;
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -325,7 +371,7 @@ __device__ __forceinline__ void seed_phase_direct(const MatchParams &p, const Se
     for (int ws = 0;; ws += stride) {
         int n;
         unsigned long long fw, rc;
-        seed_window<GEN>(p, w, lane, seg, so, n_total, pw, ws, GEN || ix.first_phase != 0, n, fw, rc);
+        seed_window<GEN>(p, w, lane, seg, so, n_total, pw, ws, GEN || ix.first_phase != 0, fw0, n, fw, rc);
         const uint32_t full = (n >= 31) ? 0xFFFFFFFFu : ((1u << (n + 1)) - 1u);
         int lo[K + 1], cnt[K + 1], per = 0;
 #pragma unroll
@@ -340,11 +386,26 @@ __device__ __forceinline__ void seed_phase_direct(const MatchParams &p, const Se
         }
         __syncwarp();                                                  // Eq tables / start states visible
         uint32_t n_ver = 0;
+        auto verify = [&](uint32_t entry, uint32_t strand, uint32_t aux, bool valid) {
+            int level = K + 1;
+            if (valid) {
+                if (ANCH) {
+                    level = seed_anchor_level1(__ldg(ix.ewords + entry), aux, w.pair_a, full, ix.two, w.init_a);
+                } else if (GEN) {
+                    const uint2 words = __ldg(ix.ewords + entry);
+                    level = seed_verify<K, BL16, true>(strand ? words.x : words.y, bl, w.pair_a + 128u, full, ix.two, w.v_a);
+                } else {
+                    const uint32_t word = __ldg(&ix.ewords[entry].x);
+                    level = seed_verify<K, BL16, false>(word, bl, w.pair_a + strand * 128u, full, ix.two, 0u);
+                }
+            }
+            seed_fold(level, entry, strand, K, ix.eids, w.list, lt_mask, best, count);
+        };
         for (int c0 = 0; c0 < 2 * per; c0 += 32) {
             const int c = c0 + lane;
             const uint32_t strand = c >= per ? 1u : 0u;
             int r = c - (strand ? per : 0);
-            uint32_t st = 0, en = 0;
+            uint32_t st = 0, en = 0, aux = 0;
             if (c < 2 * per) {
                 const unsigned long long text = strand ? fw : rc;
 #pragma unroll
@@ -356,25 +417,22 @@ __device__ __forceinline__ void seed_phase_direct(const MatchParams &p, const Se
                             const uint32_t *b = ix.boff + ix.boff_base[q] + h;
                             st = __ldg(b);
                             en = __ldg(b + 1);
+                            if (ANCH) {                               // operands of the anchored extension (see seed_precheck)
+                                const uint32_t pre = ix.pre[q], left = (pre >> 5) & 1u;
+                                const uint32_t b0 = left ? (uint32_t)(n - j) : (uint32_t)j + ((pre >> 9) & 31u);
+                                aux = (2u * (pre & 31u)) | (left << 6) | ((strand ^ left) << 7) | (b0 << 21);
+                            }
                         }
                         r -= cnt[q];
                     }
                 }
             }
+            // entry 0 of every lane's bucket, then entry 1, ..: one or two rounds (compacting the few entries into
+            // full rounds through shared memory was measured slower: the extra round trip costs more than the idle lanes)
             while (__any_sync(FULL, st < en)) {
                 const bool valid = st < en;
-                int level = K + 1;
-                if (valid) {
-                    if (GEN) {
-                        const uint2 words = __ldg(ix.ewords + st);
-                        level = seed_verify<K, BL16, true>(strand ? words.x : words.y, bl, w.pair_a + 128u, full, ix.two, w.v_a);
-                    } else {
-                        const uint32_t word = __ldg(&ix.ewords[st].x);
-                        level = seed_verify<K, BL16, false>(word, bl, w.pair_a + strand * 128u, full, ix.two, 0u);
-                    }
-                }
                 n_ver += (uint32_t)__popc(__ballot_sync(FULL, valid));
-                seed_fold(level, st, strand, K, ix.eids, w.list, lt_mask, best, count);
+                verify(st, strand, aux, valid);
                 st += valid ? 1u : 0u;
             }
         }
@@ -383,7 +441,7 @@ __device__ __forceinline__ void seed_phase_direct(const MatchParams &p, const Se
             w.cnt[1] += n_ver;
             w.cnt[2] += n_ver;
             w.cnt[3] += 1ull;
-            w.cnt[4] += (unsigned long long)(n_ver * (uint32_t)bl * (uint32_t)(2 * K + 1));
+            w.cnt[4] += (unsigned long long)(n_ver * (uint32_t)(ANCH ? 8 : bl) * (uint32_t)(2 * K + 1));
         }
         __syncwarp();
         if (!GEN || ws + SEED_MAX_LEN >= n_total) break;
@@ -407,7 +465,8 @@ __device__ __forceinline__ void seed_phase_direct(const MatchParams &p, const Se
 template <int KP, bool BL16, bool PRE, bool GEN>
 __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex &ix, const SeedWarp &w, const int lane,
                                            const int seg, const long long so, const int n_total,
-                                           const unsigned long long *__restrict__ pw, const int bl, int &best, int &count) {
+                                           const unsigned long long *__restrict__ pw, const unsigned long long fw0, const int bl,
+        int &best, int &count) {
     constexpr int K = KP;
     const int P = ix.n_pieces;
     const int stride = 32 - bl - K;                                      // GEN: window step (>= 13 for bl <= 16, K <= 3)
@@ -427,7 +486,7 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
     for (int ws = 0;; ws += stride) {                                    // windows (exactly one when !GEN)
         int n;
         unsigned long long fw, rc;
-        seed_window<GEN>(p, w, lane, seg, so, n_total, pw, ws, GEN || ix.first_phase != 0, n, fw, rc);
+        seed_window<GEN>(p, w, lane, seg, so, n_total, pw, ws, GEN || ix.first_phase != 0, fw0, n, fw, rc);
         // bucket ranges of every (strand, piece, position); the non-empty ones become slots, prefix-summed in order
         uint32_t total = 0;
         int n_slots = 0;
@@ -560,6 +619,44 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
     }
 }
 
+// store_result of the seeded kernels: tie space comes from a per-warp CHUNK of the bump-allocated tie buffer (one atomic
+// on the global cursor per SEED_TIE_CHUNK ids instead of one per matched segment; finalize gathers the lists into segment
+// order wherever they lie).  The unused tails of the chunks are why the host sizes the buffer with seed_tie_slack().
+constexpr int SEED_TIE_CHUNK = SEED_TIE_CHUNK_N;
+__device__ __forceinline__ void seed_store_result(const MatchParams &p, int seg, int lane, int K, int best, int count,
+                                                  const uint32_t *list, unsigned long long *chunk) {
+    if (count > SEED_LIST_CAP) {         // the list is incomplete: the segment is re-run with a full-size list
+        if (lane == 0) {
+            const unsigned int q = atomicAdd(&p.ctr->n_ovf, 1u);
+            p.ovf_list[q] = seg;
+            p.min_ed[seg] = best;
+            p.n_ties[seg] = 0;
+        }
+        return;
+    }
+    unsigned long long pos = 0;
+    if (lane == 0) {
+        p.min_ed[seg] = (best <= K) ? best : -1;
+        p.n_ties[seg] = count;
+        if (count > 0) {
+            unsigned long long at = chunk[0], left = chunk[1];
+            if ((unsigned long long)count > left) {
+                left = (unsigned long long)max(count, SEED_TIE_CHUNK);
+                at = atomicAdd(&p.ctr->tie_cursor, left);
+            }
+            pos = at;
+            chunk[0] = at + (unsigned long long)count;
+            chunk[1] = left - (unsigned long long)count;
+            p.tie_start[seg] = (unsigned int)pos;
+        }
+    }
+    if (count > 0) {
+        pos = __shfl_sync(FULL, pos, 0);
+        if (pos + (unsigned long long)count <= p.tie_cap)
+            for (int i = lane; i < count; i += 32) p.tie_buf[pos + i] = (int)list[i];
+    }
+}
+
 // The seeded match kernel.  One warp per segment; ITERATIVE DEEPENING over the error bound: phase k' looks for every
 // barcode within k' edits with the seeds of k' + 1 pieces (k' = 1: two 8-mers, ~12 candidates per segment at B = 25 k;
 // k' = 2: 5+5+6, ~1 100; k' = 3: four 4-mers, ~9 300) and the search stops at the first phase that finds something: the
@@ -588,6 +685,10 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : SEED_MIN_CTAS) match_s
     __shared__ __align__(16) uint32_t s_init[33][8];           // pre-check start states by boundary: R0 S0 R1 S1 R2 S2 R3 S3
     __shared__ __align__(16) uint32_t s_v[SEED_WARPS][4];      // GEN: start states of the window per level
     __shared__ unsigned long long s_cnt[SEED_WARPS][8];        // work counters (see the flush at the end)
+    __shared__ int4 s_batch[SEED_WARPS][SEED_BATCH];           // the warp's batch: segment, length, byte offset (lo, hi)
+    __shared__ unsigned long long s_text[SEED_WARPS][SEED_BATCH];   // ... and its packed text (one-window segments)
+    __shared__ int2 s_bpos[SEED_WARPS];                         // ... position inside the batch, its length
+    __shared__ unsigned long long s_tie[SEED_WARPS][2];        // the warp's chunk of the tie buffer: next position, entries left
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x < 33) {
@@ -600,6 +701,7 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : SEED_MIN_CTAS) match_s
         }
     }
     if (lane < 8) s_cnt[warp][lane] = 0ull;
+    if (lane < 2) s_tie[warp][lane] = 0ull;
     __syncthreads();
     SeedWarp w;
     w.prefix = s_prefix[warp];
@@ -624,37 +726,70 @@ __global__ void __launch_bounds__(SEED_THREADS, GEN ? 4 : SEED_MIN_CTAS) match_s
     const int *items = GEN ? p.wide_list : p.fast_list;
     const int bl = p.bl;
 
+    if (lane == 0) s_bpos[warp] = make_int2(0, 0);
+    unsigned int last_base = 0;
+    const unsigned int tail_at = gridDim.x * SEED_WARPS * 16u;          // segments left when the batches shrink to one
+    __syncwarp();
     for (;;) {
-        unsigned int idx = 0;
-        if (lane == 0) idx = atomicAdd(cursor, 1u);
-        idx = __shfl_sync(FULL, idx, 0);
-        if (idx >= n_items) break;
-        const int seg = items[idx];
-        const long long so = p.seg_off[seg] - p.b0;
-        const int n_total = (int)(p.seg_off[seg + 1] - p.b0 - so);
+        // a batch of SEED_BATCH segments per visit of the cursor: lanes 0..SEED_BATCH-1 fetch one segment's id, extent
+        // and first packed word each, so the chain atomic -> list -> offsets -> text is paid once per batch.  The position
+        // inside the batch lives in shared memory: nothing of the batching stays in registers across the phases.
+        const int2 bp = s_bpos[warp];                                  // .x = next position, .y = length of the batch
+        int g = bp.x;
+        int blen = bp.y;
+        if (g == blen) {
+            // near the end of the list a batch is one segment: a warp stuck with several expensive segments while the
+            // others run dry costs more than the batching saves (measured at -mr 3: 5 %)
+            blen = (last_base + tail_at < n_items) ? SEED_BATCH : 1;
+            unsigned int base = 0;
+            if (lane == 0) base = atomicAdd(cursor, (unsigned int)blen);
+            base = __shfl_sync(FULL, base, 0);
+            last_base = base;
+            if (lane < blen) {
+                int4 b = make_int4(-1, 0, 0, 0);
+                unsigned long long t = 0ull;
+                if (base + lane < n_items) {
+                    const int sg = items[base + lane];
+                    const long long o = p.seg_off[sg] - p.b0;
+                    b = make_int4(sg, (int)(p.seg_off[sg + 1] - p.b0 - o), (int)(unsigned int)(o & 0xFFFFFFFFll), (int)(o >> 32));
+                    if (!GEN) t = __ldg(p.pk + (o >> 5) + sg);
+                }
+                s_batch[warp][lane] = b;
+                s_text[warp][lane] = t;
+            }
+            g = 0;
+        }
+        __syncwarp();
+        if (lane == 0) s_bpos[warp] = make_int2(g + 1, blen);
+        const int4 bt = s_batch[warp][g];
+        const int seg = bt.x;
+        if (seg < 0) break;                                              // the work list is exhausted
+        const unsigned long long fw0 = s_text[warp][g];
+        const int n_total = bt.y;
+        const long long so = ((long long)bt.w << 32) | (long long)(unsigned int)bt.z;
         const unsigned long long *pw = p.pk + (so >> 5) + seg;
         int best = K + 1, count = 0;
         if constexpr (K >= 3) {
             if (ixs.run_mask & (1 << (K - 2))) {
-                if (ixs.ph[K - 2].direct) seed_phase_direct<K - 2, BL16, GEN>(p, ixs.ph[K - 2], w, lane, seg, so, n_total, pw, bl, best, count);
-                else seed_phase<K - 2, BL16, PRE, GEN>(p, ixs.ph[K - 2], w, lane, seg, so, n_total, pw, bl, best, count);
+                if (ixs.ph[K - 2].direct) seed_phase_direct<K - 2, BL16, GEN>(p, ixs.ph[K - 2], w, lane, seg, so, n_total, pw, fw0, bl, best, count);
+                else seed_phase<K - 2, BL16, PRE, GEN>(p, ixs.ph[K - 2], w, lane, seg, so, n_total, pw, fw0, bl, best, count);
                 if (best > K - 2) best = K + 1;
             }
         }
         if constexpr (K >= 2) {
             if ((ixs.run_mask & (1 << (K - 1))) && best > K) {
-                if (ixs.ph[K - 1].direct) seed_phase_direct<K - 1, BL16, GEN>(p, ixs.ph[K - 1], w, lane, seg, so, n_total, pw, bl, best, count);
-                else seed_phase<K - 1, BL16, PRE, GEN>(p, ixs.ph[K - 1], w, lane, seg, so, n_total, pw, bl, best, count);
+                if (ixs.ph[K - 1].direct) seed_phase_direct<K - 1, BL16, GEN>(p, ixs.ph[K - 1], w, lane, seg, so, n_total, pw, fw0, bl, best, count);
+                else seed_phase<K - 1, BL16, PRE, GEN>(p, ixs.ph[K - 1], w, lane, seg, so, n_total, pw, fw0, bl, best, count);
                 if (best > K - 1) best = K + 1;
             }
         }
         if (best > K) {
-            if (ixs.ph[K].direct) seed_phase_direct<K, BL16, GEN>(p, ixs.ph[K], w, lane, seg, so, n_total, pw, bl, best, count);
-            else seed_phase<K, BL16, PRE, GEN>(p, ixs.ph[K], w, lane, seg, so, n_total, pw, bl, best, count);
+            if (ixs.ph[K].direct) seed_phase_direct<K, BL16, GEN>(p, ixs.ph[K], w, lane, seg, so, n_total, pw, fw0, bl, best, count);
+            else seed_phase<K, BL16, PRE, GEN>(p, ixs.ph[K], w, lane, seg, so, n_total, pw, fw0, bl, best, count);
         }
         // more hits than the list holds (in GEN mode possibly only duplicates from overlapping windows): exact re-run
         if (count <= SEED_LIST_CAP) count = sort_unique(w.list, w.tmp, count, lane);
-        store_result(p, seg, lane, K, best, count, w.list, SEED_LIST_CAP, true);
+        seed_store_result(p, seg, lane, K, best, count, w.list, s_tie[warp]);
         __syncwarp();
     }
     if (lane == 0) {
