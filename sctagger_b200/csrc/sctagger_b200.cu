@@ -71,6 +71,7 @@ struct sct_handle {
     uint2 *d_ewords[3] = {nullptr, nullptr, nullptr};
     SeedIndex seed_by_k[4] = {};  // index of error bound k (k = 0 only when -mr 0), built in sct_create for k = 1..K
     bool seed_pre_by_k[4] = {false, false, false, false};   // the anchored pre-check is possible for this bound
+    int chain_kernels = 1;        // option: a chunk's kernels start behind the previous chunk's match kernel
     int seed_deepening = 1;       // option: search error bounds 1, 2, .. K in turn and stop at the first hit
     int seed_direct_opt = -1;     // option seed_direct: -1 auto (sparse indexes), 0 never, 1 every phase
     int seed_prefilter_opt = -1;  // option seed_prefilter: -1 auto (per phase, by expected bucket size), 0 off, 1 on where possible
@@ -314,7 +315,7 @@ int enqueue_pass(sct_handle *h, Slot &s, int64_t n, Slot *prev = nullptr) {
     // leaving the GPU to themselves; only the finalize, which advances the running tie base, waits for that chunk's
     // finalize (ev_end).  Without any ordering the two streams run both chunks' persistent kernels side by side, they
     // finish together, and the GPU idles while the host handles one chunk and prepares the next.
-    const bool chained = prev && prev->busy;
+    const bool chained = prev && prev->busy && h->chain_kernels;
     if (chained) CUDA_TRY(cudaStreamWaitEvent(s.stream, fk ? prev->ev_k1 : prev->ev_end, 0));
     const int path = h->use_dp || h->path_override == 2 ? 2 : (fk ? 0 : 1);
     MatchParams p = make_params(h, s);
@@ -722,7 +723,7 @@ int sct_create(int device, const uint8_t *barcodes, int32_t n_barcodes, int32_t 
     h->chunk_segs = segs;
     h->chunk_bytes = segs * 40;
     // streamed chunks are kept small enough that staging / copies of one chunk overlap the kernels of the other slot
-    h->stream_segs = std::min<int64_t>(segs, 1 << 19);
+    h->stream_segs = std::min<int64_t>(segs, 1 << 20);
     // the table uploads above are pageable cudaMemcpy's on the legacy stream; the kernels run on non-blocking streams
     CUDA_TRY(cudaDeviceSynchronize());
     *out = h;
@@ -776,6 +777,8 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "seed_prefilter") {
         if (value > 0 && !h->seed_pre_ok) return fail(SCT_E_ARG, "seed_prefilter is not available for this barcode length / -mr");
         h->seed_prefilter_opt = value < 0 ? -1 : (value != 0 ? 1 : 0);   // -1 auto, 0 off, 1 on wherever possible
+    } else if (k == "chain_kernels") {
+        h->chain_kernels = value != 0 ? 1 : 0;
     } else if (k == "seed_direct") {        // -1 auto, 0 slot-table path for every phase, 1 per-lane path for every phase
         h->seed_direct_opt = value < 0 ? -1 : (value != 0 ? 1 : 0);
     } else if (k == "seed_deepening") {     // 1 (default): error bounds 1..K in turn, stop at the first hit; 0: bound K only
@@ -875,7 +878,7 @@ static int match_impl(sct_handle *h, const uint8_t *seg_bytes, const int64_t *se
     int64_t ramp = std::min<int64_t>(h->stream_segs, h->ramp_segs);
     while (first < n) {
         int64_t cn = std::min<int64_t>(std::min(h->stream_segs, ramp), n - first);
-        ramp = std::min<int64_t>(h->stream_segs, ramp * 2);
+        ramp = std::min<int64_t>(h->stream_segs, ramp * 4);   // 32 k, 128 k, 512 k, then full chunks: every chunk costs ~70 us of kernel tail + launch gaps
         const int64_t limit = seg_offsets[first] + h->chunk_bytes;
         if (seg_offsets[first + cn] > limit) {
             const int64_t *e = std::upper_bound(seg_offsets + first, seg_offsets + first + cn + 1, limit);

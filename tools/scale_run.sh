@@ -1,11 +1,14 @@
 #!/bin/bash
-# 1/2/4/8-GPU weak-scaling run of bench.py, launched the way the driver launches it (one rank per GPU, torchrun).
-for n in 1 2 4 8; do
-  if [ $n -eq 1 ]; then python bench.py --gpus 1 --no-cpu > gpurun_out/scale_$n.json 2> gpurun_out/scale_$n.err
+# bench.py at the GPU counts given on the command line (default 1 2 4 8), launched the way the driver launches it (one rank
+# per GPU, torchrun).  BASELINE configs[2]: ONE 10 M-segment input sharded over the ranks (strong scaling).
+set -u
+mkdir -p gpurun_out
+for n in ${@:-1 2 4 8}; do
+  if [ $n -eq 1 ]; then python bench.py --gpus 1 --no-cpu --no-secondary > gpurun_out/scale_$n.json 2> gpurun_out/scale_$n.err
   else python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n > gpurun_out/scale_$n.json 2> gpurun_out/scale_$n.err; fi
   python -c "
 import json,sys
 d=json.loads([l for l in open('gpurun_out/scale_$n.json') if l.startswith('{')][-1])
-print($n, 'value', round(d['value']/1e6,1), 'M/s  e2e', round(d['e2e']['value']/1e6,1), 'M/s  ms', round(d['ms_per_step'],3), d['clocks']['sm_mhz'], d['clocks']['reasons'])"
+print($n, 'value', round(d['value']/1e6,1), 'M/s  e2e', round(d['e2e']['value']/1e6,1), 'M/s  pageable', round(d['e2e']['pageable']['value']/1e6,1), ' ms', round(d['ms_per_step'],3), d['clocks']['sm_mhz'], d['clocks']['reasons'], d['check']['sha256'][:10], d['check']['sharded_equals_single_gpu'])"
 done
 nproc
