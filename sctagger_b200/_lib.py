@@ -238,6 +238,26 @@ class ResultBuffers:
             x.close()
 
 
+class AlignBuffers:
+    """Caller-owned, reusable, page-locked result arrays for Aligner.align(..., out=...): strand, dist and loc_offsets are
+    written by the device directly.  Capacity in reads."""
+
+    def __init__(self, capacity: int):
+        self.capacity = int(capacity)
+        self._strand = Pinned(max(self.capacity, 1), np.int8)
+        self._dist = Pinned(max(self.capacity, 1), np.int32)
+        self._locoff = Pinned(self.capacity + 1, np.int64)
+
+    def views(self, n):
+        if n > self.capacity:
+            raise ValueError(f"AlignBuffers of capacity {self.capacity} cannot hold {n} reads")
+        return self._strand.array[:max(n, 1)], self._dist.array[:max(n, 1)], self._locoff.array[:n + 1]
+
+    def close(self):
+        for x in (self._strand, self._dist, self._locoff):
+            x.close()
+
+
 class Matcher:
     """One handle = one GPU with the barcode table resident (sct_create .. sct_destroy)."""
 
@@ -380,21 +400,32 @@ class Aligner:
     def __exit__(self, *exc):
         self.close()
 
-    def align(self, read_bytes: np.ndarray, offsets: np.ndarray):
-        """-> (strand int8[n] ('+'/'-' as ASCII, 0 = NA), dist int32[n] (-1 = NA), loc_offsets int64[n+1], locs int32[])"""
+    def align(self, read_bytes: np.ndarray, offsets: np.ndarray, out: "AlignBuffers" = None, copy_locs: bool = True):
+        """-> (strand int8[n] ('+'/'-' as ASCII, 0 = NA), dist int32[n] (-1 = NA), loc_offsets int64[n+1], locs int32[]).
+        Arrays in page-locked memory (`Pinned`, `AlignBuffers`) are copied from / to directly; pageable numpy arrays are
+        staged by the library's host threads.  With copy_locs=False, locs is a view of the library-owned buffer, valid
+        until the next call on this Aligner."""
         rb = _as_u8(read_bytes)
         off = np.ascontiguousarray(offsets, dtype=np.int64)
         n = off.shape[0] - 1
-        strand = np.empty(max(n, 1), dtype=np.int8)
-        dist = np.empty(max(n, 1), dtype=np.int32)
-        loc_off = np.empty(n + 1, dtype=np.int64)
+        if out is None:
+            strand = np.empty(max(n, 1), dtype=np.int8)
+            dist = np.empty(max(n, 1), dtype=np.int32)
+            loc_off = np.empty(n + 1, dtype=np.int64)
+        else:
+            strand, dist, loc_off = out.views(n)
         ids = _i32p()
         total = ctypes.c_int64(0)
         _check(lib().sct_align(self._h, _ptr(rb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), n,
                                _ptr(strand, ctypes.c_int8), _ptr(dist, ctypes.c_int32), _ptr(loc_off, ctypes.c_int64),
                                ctypes.byref(ids), ctypes.byref(total)))
         t = int(total.value)
-        locs = np.ctypeslib.as_array(ids, shape=(t,)).copy() if t else np.zeros(0, dtype=np.int32)
+        if t == 0:
+            locs = np.zeros(0, dtype=np.int32)
+        elif copy_locs:
+            locs = np.ctypeslib.as_array(ids, shape=(t,)).copy()
+        else:
+            locs = np.ctypeslib.as_array(ids, shape=(t,))
         return strand[:n], dist[:n], loc_off, locs
 
     def stage(self, read_bytes: np.ndarray, offsets: np.ndarray):

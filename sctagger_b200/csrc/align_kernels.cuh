@@ -27,7 +27,8 @@ constexpr int ALN_BUCKETS = 1024;        // length buckets of 32 bases; longer r
 
 struct AlignParams {
     const uint8_t *bytes;                // read bytes of the chunk; the allocation is 16-byte aligned and padded
-    const long long *off;                // n + 1 offsets
+    const long long *off;                // n + 1 offsets in the CALLER's numbering: byte j of the chunk is offset b0 + j
+    long long b0, nbytes;
     int n;
     int m;                               // adapter length (<= 32)
     const uint2 *peq;                    // [256] {Eq of a1, Eq of a2} by byte value
@@ -49,12 +50,17 @@ __device__ __forceinline__ int len_bucket(long long len) {
     return ALN_BUCKETS - 1 - (int)(b < ALN_BUCKETS - 1 ? b : ALN_BUCKETS - 1);   // descending length
 }
 
-__global__ void __launch_bounds__(256) aln_hist_kernel(const long long *__restrict__ off, int n, unsigned int *__restrict__ hist) {
+// also validates the offsets (non-decreasing, inside the chunk): *bad counts the reads that are not — the call fails
+__global__ void __launch_bounds__(256) aln_hist_kernel(const long long *__restrict__ off, int n, long long b0, long long nbytes,
+                                                       unsigned int *__restrict__ hist, unsigned int *__restrict__ bad) {
     __shared__ unsigned int sh[ALN_BUCKETS];
     for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x) sh[i] = 0;
     __syncthreads();
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        atomicAdd(&sh[len_bucket(off[i + 1] - off[i])], 1u);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const long long a = off[i] - b0, b = off[i + 1] - b0;
+        if (a < 0 || b < a || b > nbytes) atomicAdd(bad, 1u);
+        atomicAdd(&sh[len_bucket(b > a ? b - a : 0)], 1u);
+    }
     __syncthreads();
     for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x)
         if (sh[i]) atomicAdd(&hist[i], sh[i]);
@@ -79,7 +85,8 @@ __global__ void __launch_bounds__(256) aln_scatter_kernel(const long long *__res
                                                           int *__restrict__ order) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    order[atomicAdd(&cursor[len_bucket(off[i + 1] - off[i])], 1u)] = i;
+    const long long len = off[i + 1] - off[i];
+    order[atomicAdd(&cursor[len_bucket(len > 0 ? len : 0)], 1u)] = i;
 }
 
 // the same counting sort keyed by an int array (pass 2: columns each read still has to scan)
@@ -98,6 +105,14 @@ __global__ void __launch_bounds__(256) aln_scatter_work_kernel(const int *__rest
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     order[atomicAdd(&cursor[len_bucket(work[i])], 1u)] = i;
+}
+
+// extent of read r inside the chunk's byte buffer (clamped: bad offsets fail the call, they must not leave the buffer)
+__device__ __forceinline__ void read_extent(const AlignParams &p, int r, long long &beg, long long &end) {
+    beg = p.off[r] - p.b0;
+    end = p.off[r + 1] - p.b0;
+    beg = beg < 0 ? 0 : (beg > p.nbytes ? p.nbytes : beg);
+    end = end < beg ? beg : (end > p.nbytes ? p.nbytes : end);
 }
 
 // ---- Myers column ---------------------------------------------------------------------------------------------------
@@ -151,7 +166,8 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass1_kernel(const AlignParam
     const int t = blockIdx.x * ALN_THREADS + threadIdx.x;
     if (t >= p.n) return;
     const int r = p.order[t];
-    const long long beg = p.off[r], end = p.off[r + 1];
+    long long beg, end;
+    read_extent(p, r, beg, end);
     const int m = p.m;
     const uint32_t top = 1u << (m - 1);
     Myers a, b;
@@ -207,7 +223,8 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass2_kernel(const AlignParam
     const int r = p.order[t];
     const int nl = p.n_locs[r];
     if (nl == 0 || p.work[r] > ALN_LONG_WORK) return;             // long spans: aln_pass2_long_kernel, one warp each
-    const long long beg = p.off[r], end = p.off[r + 1];
+    long long beg, end;
+    read_extent(p, r, beg, end);
     const long long out0 = p.loc_off[r];
     if ((unsigned long long)(out0 + nl) > p.loc_cap) return;      // the host grows the buffer and repeats the pass
     const int m = p.m, d = p.dist[r];
@@ -246,7 +263,8 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass2_long_kernel(const Align
     const int r = p.order[w];                                     // descending work: the long ones come first
     const int nl = p.n_locs[r];
     if (nl == 0 || p.work[r] <= ALN_LONG_WORK) return;
-    const long long beg = p.off[r], end = p.off[r + 1];
+    long long beg, end;
+    read_extent(p, r, beg, end);
     const long long out0 = p.loc_off[r];
     if ((unsigned long long)(out0 + nl) > p.loc_cap) return;
     const int m = p.m, d = p.dist[r];
@@ -307,7 +325,9 @@ __global__ void __launch_bounds__(1024) aln_block_sums_kernel(const int *__restr
 }
 
 // single block: exclusive prefix of the block sums in place, grand total to *total
-__global__ void __launch_bounds__(1024) aln_block_prefix_kernel(long long *__restrict__ block_sums, int n_blocks, long long *__restrict__ total) {
+// total[0] = locations of this chunk, total[1] = locations of all earlier chunks of the call (`run`, advanced here)
+__global__ void __launch_bounds__(1024) aln_block_prefix_kernel(long long *__restrict__ block_sums, int n_blocks, long long *__restrict__ total,
+                                                                long long *__restrict__ run) {
     __shared__ long long sh[1024];
     __shared__ long long carry;
     if (threadIdx.x == 0) carry = 0;
@@ -330,12 +350,19 @@ __global__ void __launch_bounds__(1024) aln_block_prefix_kernel(long long *__res
         if (threadIdx.x == 1023) carry = c + incl;
         __syncthreads();
     }
-    if (threadIdx.x == 0) *total = carry;
+    if (threadIdx.x == 0) {
+        const long long b = *run;
+        total[0] = carry;
+        total[1] = b;
+        *run = b + carry;
+    }
 }
 
 __global__ void __launch_bounds__(1024) aln_scan_apply_kernel(const int *__restrict__ n_locs, int n,
                                                               const long long *__restrict__ block_prefix,
-                                                              long long *__restrict__ loc_off) {
+                                                              long long *__restrict__ loc_off /* chunk-local: pass 2 */,
+                                                              long long *__restrict__ loc_off_out /* the call's numbering */,
+                                                              const long long *__restrict__ total) {
     __shared__ long long warp_sums[32];
     const int i = blockIdx.x * 1024 + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -361,8 +388,13 @@ __global__ void __launch_bounds__(1024) aln_scan_apply_kernel(const int *__restr
     __syncthreads();
     const long long excl = block_prefix[blockIdx.x] + warp_sums[warp] + incl - c;
     if (i < n) {
+        const long long base = total[1];
         loc_off[i] = excl;
-        if (i == n - 1) loc_off[n] = excl + c;
+        loc_off_out[i] = base + excl;
+        if (i == n - 1) {
+            loc_off[n] = excl + c;
+            loc_off_out[n] = base + excl + c;
+        }
     }
 }
 

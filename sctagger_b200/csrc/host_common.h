@@ -157,6 +157,22 @@ inline void par_memcpy(HostPool *pool, void *dst, const void *src, size_t bytes)
     });
 }
 
+// Is [p, p + bytes) page-locked host memory the copy engines can read / write directly?
+inline bool is_pinned(const void *p, size_t bytes) {
+    if (!p || bytes == 0) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    if (a.type != cudaMemoryTypeHost) return false;
+    if (cudaPointerGetAttributes(&a, (const char *)p + bytes - 1) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
 template <class T>
 void dev_free(T *&p) {
     if (p) cudaFree(p);

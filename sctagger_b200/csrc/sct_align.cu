@@ -11,13 +11,14 @@ using namespace scth;
 namespace {
 
 struct ASlot {
-    int64_t cap_reads = 0, cap_bytes = 0, cap_locs = 0;
+    int64_t cap_reads = 0, cap_bytes = 0, cap_locs = 0, cap_hbytes = 0;
     uint8_t *h_bytes = nullptr;
     long long *h_off = nullptr, *h_locoff = nullptr, *h_total = nullptr;
     signed char *h_strand = nullptr;
     int *h_dist = nullptr, *h_locs = nullptr;
     uint8_t *d_bytes = nullptr;
-    long long *d_off = nullptr, *d_locoff = nullptr, *d_bsums = nullptr, *d_total = nullptr;
+    long long *d_off = nullptr, *d_locoff = nullptr, *d_locoff_out = nullptr, *d_bsums = nullptr, *d_total = nullptr;
+    unsigned int *d_bad = nullptr, *h_bad = nullptr;
     unsigned int *d_hist = nullptr;
     int *d_order = nullptr, *d_dist = nullptr, *d_nlocs = nullptr, *d_locs = nullptr;
     int2 *d_span = nullptr;
@@ -26,7 +27,12 @@ struct ASlot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
     int64_t n = 0, nbytes = 0, first = 0;
+    long long b0 = 0;                   // offset of the chunk's first byte in the caller's numbering
     bool busy = false;
+    // where the fixed-size results go: the caller's arrays when they are page-locked, else the slot's staging
+    signed char *dst_strand = nullptr;
+    int *dst_dist = nullptr;
+    long long *dst_locoff = nullptr;
 };
 
 }  // namespace
@@ -38,7 +44,10 @@ struct sct_align_handle {
     int64_t chunk_bytes = 0, chunk_reads = 0;
     HostPool *pool = nullptr;
     ASlot slot[2];
-    std::vector<int32_t> locs_host;
+    int32_t *locs_pinned = nullptr;     // locations of the whole call (library-owned, page-locked; sct_align's *locs)
+    int64_t locs_cap = 0;
+    long long *d_run = nullptr;         // device-side running sum of locations over the chunks of one call
+    bool in_bytes_pinned = false, in_off_pinned = false, out_strand_pinned = false, out_dist_pinned = false, out_locoff_pinned = false;
     int64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool staged = false;
 };
@@ -47,40 +56,41 @@ namespace {
 
 void free_aslot(ASlot &s) {
     host_free(s.h_bytes); host_free(s.h_off); host_free(s.h_locoff); host_free(s.h_total); host_free(s.h_strand);
-    host_free(s.h_dist); host_free(s.h_locs);
+    host_free(s.h_dist); host_free(s.h_locs); host_free(s.h_bad);
+    dev_free(s.d_bad); dev_free(s.d_locoff_out);
     dev_free(s.d_bytes); dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_bsums); dev_free(s.d_total);
     dev_free(s.d_hist); dev_free(s.d_order); dev_free(s.d_dist); dev_free(s.d_nlocs); dev_free(s.d_locs); dev_free(s.d_span); dev_free(s.d_work);
     dev_free(s.d_strand);
-    s.cap_reads = s.cap_bytes = s.cap_locs = 0;
+    s.cap_reads = s.cap_bytes = s.cap_locs = s.cap_hbytes = 0;
 }
 
 int ensure_locs(ASlot &s, int64_t want) {
     if (want <= s.cap_locs) return SCT_OK;
     const int64_t c = std::max<int64_t>(want + want / 4, 4096);
-    host_free(s.h_locs);
     dev_free(s.d_locs);
     s.cap_locs = 0;
     CUDA_TRY(cudaMalloc(&s.d_locs, (size_t)c * sizeof(int)));
-    CUDA_TRY(cudaMallocHost(&s.h_locs, (size_t)c * sizeof(int)));
     s.cap_locs = c;
     return SCT_OK;
 }
 
-int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes) {
+int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes, bool stage_bytes) {
     if (!s.stream) {
         CUDA_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CUDA_TRY(cudaEventCreate(&s.ev0));
         CUDA_TRY(cudaEventCreate(&s.ev1));
         CUDA_TRY(cudaEventCreate(&s.ev2));
         CUDA_TRY(cudaEventCreate(&s.ev3));
-        CUDA_TRY(cudaMallocHost(&s.h_total, sizeof(long long)));
-        CUDA_TRY(cudaMalloc(&s.d_total, sizeof(long long)));
+        CUDA_TRY(cudaMallocHost(&s.h_total, 2 * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_total, 2 * sizeof(long long)));
+        CUDA_TRY(cudaMallocHost(&s.h_bad, sizeof(unsigned int)));
+        CUDA_TRY(cudaMalloc(&s.d_bad, sizeof(unsigned int)));
         CUDA_TRY(cudaMalloc(&s.d_hist, ALN_BUCKETS * sizeof(unsigned int)));
     }
     if (reads > s.cap_reads) {
         const int64_t c = std::max<int64_t>(reads, 1024);
         host_free(s.h_off); host_free(s.h_locoff); host_free(s.h_strand); host_free(s.h_dist);
-        dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_bsums); dev_free(s.d_order); dev_free(s.d_dist);
+        dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_locoff_out); dev_free(s.d_bsums); dev_free(s.d_order); dev_free(s.d_dist);
         dev_free(s.d_nlocs); dev_free(s.d_strand); dev_free(s.d_span); dev_free(s.d_work);
         s.cap_reads = 0;
         CUDA_TRY(cudaMallocHost(&s.h_off, (size_t)(c + 1) * sizeof(long long)));
@@ -89,6 +99,7 @@ int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes) {
         CUDA_TRY(cudaMallocHost(&s.h_dist, (size_t)c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_off, (size_t)(c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_locoff, (size_t)(c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&s.d_locoff_out, (size_t)(c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_bsums, (size_t)((c + 1023) / 1024 + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_order, (size_t)c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_dist, (size_t)c * sizeof(int)));
@@ -101,12 +112,17 @@ int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes) {
     }
     if (bytes > s.cap_bytes) {
         const int64_t c = std::max<int64_t>(bytes, 4096);
-        host_free(s.h_bytes);
         dev_free(s.d_bytes);
         s.cap_bytes = 0;
-        CUDA_TRY(cudaMallocHost(&s.h_bytes, (size_t)c + 64));
         CUDA_TRY(cudaMalloc(&s.d_bytes, (size_t)c + 64));
         s.cap_bytes = c;
+    }
+    if (stage_bytes && bytes > s.cap_hbytes) {         // pinned staging only for pageable caller buffers
+        const int64_t c = std::max<int64_t>(bytes, 4096);
+        host_free(s.h_bytes);
+        s.cap_hbytes = 0;
+        CUDA_TRY(cudaMallocHost(&s.h_bytes, (size_t)c + 64));
+        s.cap_hbytes = c;
     }
     return SCT_OK;
 }
@@ -115,6 +131,8 @@ AlignParams make_aparams(sct_align_handle *h, ASlot &s) {
     AlignParams p;
     p.bytes = s.d_bytes;
     p.off = s.d_off;
+    p.b0 = s.b0;
+    p.nbytes = s.nbytes;
     p.n = (int)s.n;
     p.m = h->m;
     p.peq = h->d_peq;
@@ -138,36 +156,39 @@ int enqueue_pass1(sct_align_handle *h, ASlot &s) {
     if (n > 0) {
         const AlignParams p = make_aparams(h, s);
         CUDA_TRY(cudaMemsetAsync(s.d_hist, 0, ALN_BUCKETS * sizeof(unsigned int), s.stream));
-        aln_hist_kernel<<<std::min((n + 255) / 256, 1184), 256, 0, s.stream>>>(s.d_off, n, s.d_hist);
+        CUDA_TRY(cudaMemsetAsync(s.d_bad, 0, sizeof(unsigned int), s.stream));
+        aln_hist_kernel<<<std::min((n + 255) / 256, 1184), 256, 0, s.stream>>>(s.d_off, n, s.b0, s.nbytes, s.d_hist, s.d_bad);
         aln_bucket_scan_kernel<<<1, ALN_BUCKETS, 0, s.stream>>>(s.d_hist);
         aln_scatter_kernel<<<(n + 255) / 256, 256, 0, s.stream>>>(s.d_off, n, s.d_hist, s.d_order);
         aln_pass1_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
         const int nb = (n + 1023) / 1024;
         aln_block_sums_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums);
-        aln_block_prefix_kernel<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total);
-        aln_scan_apply_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums, s.d_locoff);
+        aln_block_prefix_kernel<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total, h->d_run);
+        aln_scan_apply_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums, s.d_locoff, s.d_locoff_out, s.d_total);
         CUDA_TRY(cudaGetLastError());
         h->stats[0] += 7;
     } else {
-        CUDA_TRY(cudaMemsetAsync(s.d_total, 0, sizeof(long long), s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.d_total, 0, 2 * sizeof(long long), s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.d_bad, 0, sizeof(unsigned int), s.stream));
     }
     CUDA_TRY(cudaEventRecord(s.ev1, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.h_total, s.d_total, sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_total, s.d_total, 2 * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.h_bad, s.d_bad, sizeof(unsigned int), cudaMemcpyDeviceToHost, s.stream));
     return SCT_OK;
 }
 
 int enqueue_fixed_copies(ASlot &s) {
     const int64_t n = s.n;
     if (n <= 0) return SCT_OK;
-    CUDA_TRY(cudaMemcpyAsync(s.h_strand, s.d_strand, (size_t)n, cudaMemcpyDeviceToHost, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.h_dist, s.d_dist, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.h_locoff, s.d_locoff, (size_t)(n + 1) * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.dst_strand, s.d_strand, (size_t)n, cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.dst_dist, s.d_dist, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.dst_locoff, s.d_locoff_out, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
     return SCT_OK;
 }
 
 // after pass 1 has finished: size the location buffer, run pass 2
-int enqueue_pass2(sct_align_handle *h, ASlot &s, bool copy_back) {
-    const long long total = s.n > 0 ? *s.h_total : 0;
+int enqueue_pass2(sct_align_handle *h, ASlot &s, int32_t *copy_back /* where the chunk's locations go on the host, or null */) {
+    const long long total = s.n > 0 ? s.h_total[0] : 0;
     TRY(ensure_locs(s, total));
     CUDA_TRY(cudaEventRecord(s.ev2, s.stream));
     if (total > 0) {
@@ -183,37 +204,50 @@ int enqueue_pass2(sct_align_handle *h, ASlot &s, bool copy_back) {
         aln_pass2_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
         CUDA_TRY(cudaGetLastError());
         h->stats[0] += 5;
-        if (copy_back)
-            CUDA_TRY(cudaMemcpyAsync(s.h_locs, s.d_locs, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        if (copy_back != nullptr)
+            CUDA_TRY(cudaMemcpyAsync(copy_back, s.d_locs, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
     }
     CUDA_TRY(cudaEventRecord(s.ev3, s.stream));
     return SCT_OK;
 }
 
+// H2D of chunk [first, first + n).  Page-locked caller arrays are copied from directly; pageable ones go through the slot's
+// pinned staging (host threads).  The offsets travel as they are (the kernels subtract b0 and validate them).
 int stage_chunk(sct_align_handle *h, ASlot &s, const uint8_t *bytes, const int64_t *off, int64_t first, int64_t n) {
     const int64_t b0 = off[first], nbytes = off[first + n] - b0;
     if (nbytes < 0) return fail(SCT_E_ARG, "read_offsets must be non-decreasing (chunk starting at read %lld)", (long long)first);
-    TRY(ensure_aslot(s, n, nbytes));
-    if (nbytes > 0) par_memcpy(h->pool, s.h_bytes, bytes + b0, (size_t)nbytes);
-    std::atomic<bool> bad(false);
-    long long *dst = s.h_off;
-    const int64_t *src = off + first;
-    par_ranges(h->pool, n + 1, 1 << 16, [&](int64_t a, int64_t b) {
-        bool mine = false;
-        for (int64_t i = a; i < b; ++i) {
-            dst[i] = src[i] - b0;
-            if (i < n && src[i + 1] < src[i]) mine = true;
-        }
-        if (mine) bad = true;
-    });
-    if (bad) return fail(SCT_E_ARG, "read_offsets must be non-decreasing (chunk starting at read %lld)", (long long)first);
+    TRY(ensure_aslot(s, n, nbytes, !h->in_bytes_pinned));
+    const uint8_t *src_bytes = bytes + b0;
+    const long long *src_off = reinterpret_cast<const long long *>(off + first);
+    if (!h->in_bytes_pinned && nbytes > 0) {
+        par_memcpy(h->pool, s.h_bytes, src_bytes, (size_t)nbytes);
+        src_bytes = s.h_bytes;
+    }
+    if (!h->in_off_pinned) {
+        par_memcpy(h->pool, s.h_off, src_off, (size_t)(n + 1) * sizeof(long long));
+        src_off = s.h_off;
+    }
     s.n = n;
     s.nbytes = nbytes;
     s.first = first;
-    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
-    CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
+    s.b0 = b0;
+    if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, src_bytes, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.d_off, src_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
     h->stats[2] += nbytes + (n + 1) * (int64_t)sizeof(long long);
     h->stats[1] += 1;
+    return SCT_OK;
+}
+
+// The library-owned pinned buffer holding the locations of the whole call grows geometrically and keeps its content.
+int ensure_call_locs(sct_align_handle *h, int64_t need, int64_t keep) {
+    if (need <= h->locs_cap) return SCT_OK;
+    const int64_t cap = std::max<int64_t>({need, 2 * h->locs_cap, (int64_t)1 << 16});
+    int32_t *fresh = nullptr;
+    CUDA_TRY(cudaMallocHost(&fresh, (size_t)cap * sizeof(int32_t)));
+    if (keep > 0) par_memcpy(h->pool, fresh, h->locs_pinned, (size_t)keep * sizeof(int32_t));
+    host_free(h->locs_pinned);
+    h->locs_pinned = fresh;
+    h->locs_cap = cap;
     return SCT_OK;
 }
 
@@ -253,6 +287,9 @@ int sct_align_create(int device, const uint8_t *adapter, int32_t adapter_length,
     CUDA_TRY(cudaMalloc(&h->d_rpeq2, 256 * sizeof(uint32_t)));
     CUDA_TRY(cudaMemcpy(h->d_peq, peq.data(), 256 * sizeof(uint2), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(h->d_rpeq2, rpeq2.data(), 256 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMalloc(&h->d_run, sizeof(long long)));
+    CUDA_TRY(cudaMemset(h->d_run, 0, sizeof(long long)));
+    CUDA_TRY(cudaDeviceSynchronize());   // the uploads above are on the legacy stream, the kernels on non-blocking streams
     const double budget = mem_gb * (double)(1ull << 30);
     // 128 MiB chunks: one thread walks one read, so a pass cannot be shorter than its longest read (~0.3 ms for 5 kb);
     // smaller chunks pay that floor too often, one single chunk would not overlap staging / copies with the kernels
@@ -276,6 +313,8 @@ int sct_align_destroy(sct_align_handle *h) {
     }
     dev_free(h->d_peq);
     dev_free(h->d_rpeq2);
+    dev_free(h->d_run);
+    host_free(h->locs_pinned);
     delete h->pool;
     delete h;
     return SCT_OK;
@@ -302,50 +341,73 @@ int sct_align_stats(sct_align_handle *h, int64_t stats[8]) {
     return SCT_OK;
 }
 
+static int align_impl(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *read_offsets, int64_t n, int8_t *strand,
+                      int32_t *dist, int64_t *loc_offsets, const int32_t **locs, int64_t *n_locs);
+
 int sct_align(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *read_offsets, int64_t n, int8_t *strand,
               int32_t *dist, int64_t *loc_offsets, const int32_t **locs, int64_t *n_locs) {
+    const int rc = align_impl(h, read_bytes, read_offsets, n, strand, dist, loc_offsets, locs, n_locs);
+    if (rc != SCT_OK && h) {
+        // a call that failed half way leaves chunks in flight: drain them so that the handle stays usable
+        const std::string keep = g_err;
+        for (ASlot &s : h->slot) {
+            if (s.stream) cudaStreamSynchronize(s.stream);
+            s.busy = false;
+        }
+        cudaGetLastError();
+        g_err = keep;
+    }
+    return rc;
+}
+
+static int align_impl(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *read_offsets, int64_t n, int8_t *strand,
+                      int32_t *dist, int64_t *loc_offsets, const int32_t **locs, int64_t *n_locs) {
     if (!h) return fail(SCT_E_ARG, "NULL handle");
     if (n < 0) return fail(SCT_E_ARG, "n < 0");
     if (!read_offsets || !loc_offsets || !locs || !n_locs || (n > 0 && (!strand || !dist))) return fail(SCT_E_ARG, "NULL argument");
     if (n > 0 && !read_bytes && read_offsets[n] > read_offsets[0]) return fail(SCT_E_ARG, "read_bytes is NULL");
     CUDA_TRY(cudaSetDevice(h->device));
     memset(h->stats, 0, sizeof h->stats);
-    h->locs_host.clear();
     h->staged = false;
-    int64_t loc_base = 0;
+    // page-locked caller arrays (sct_host_alloc / sct_host_register / cudaHostAlloc) are copied from and to directly
+    const int64_t all_bytes = n > 0 ? read_offsets[n] - read_offsets[0] : 0;
+    h->in_bytes_pinned = all_bytes > 0 && is_pinned(read_bytes + read_offsets[0], (size_t)all_bytes);
+    h->in_off_pinned = n > 0 && is_pinned(read_offsets, (size_t)(n + 1) * sizeof(int64_t));
+    h->out_strand_pinned = n > 0 && is_pinned(strand, (size_t)n);
+    h->out_dist_pinned = n > 0 && is_pinned(dist, (size_t)n * sizeof(int32_t));
+    h->out_locoff_pinned = n > 0 && is_pinned(loc_offsets, (size_t)(n + 1) * sizeof(int64_t));
+    NvtxRange nv_call("sct_align");
+    int64_t loc_total = 0;
 
     auto finish = [&](int si) -> int {
         ASlot &s = h->slot[si];
         if (!s.busy) return SCT_OK;
+        NvtxRange nv("sct_align: wait + pass 2 + D2H");
         CUDA_TRY(cudaStreamSynchronize(s.stream));            // pass 1, total and the fixed-size results are back
-        TRY(enqueue_pass2(h, s, true));
-        CUDA_TRY(cudaStreamSynchronize(s.stream));
         const int64_t cn = s.n;
-        const long long total = cn > 0 ? *s.h_total : 0;
+        if (cn > 0 && *s.h_bad)
+            return fail(SCT_E_ARG, "read_offsets must be non-decreasing (chunk starting at read %lld: %u bad reads)",
+                        (long long)s.first, *s.h_bad);
+        const long long total = cn > 0 ? s.h_total[0] : 0, base = cn > 0 ? s.h_total[1] : 0;
+        if (total > 0) TRY(ensure_call_locs(h, base + total, base));
+        TRY(enqueue_pass2(h, s, total > 0 ? h->locs_pinned + base : nullptr));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
         float a = 0.f, b = 0.f;
         cudaEventElapsedTime(&a, s.ev0, s.ev1);
         cudaEventElapsedTime(&b, s.ev2, s.ev3);
         h->stats[4] += (int64_t)((a + b) * 1e6);
         h->stats[3] += cn * 13 + 8 + total * 4;
         if (cn > 0) {
-            par_memcpy(h->pool, strand + s.first, s.h_strand, (size_t)cn);
-            par_memcpy(h->pool, dist + s.first, s.h_dist, (size_t)cn * sizeof(int));
-            int64_t *dst = loc_offsets + s.first;
-            const long long *src = s.h_locoff;
-            par_ranges(h->pool, cn, 1 << 16, [&](int64_t x, int64_t y) {
-                for (int64_t i = x; i < y; ++i) dst[i] = loc_base + src[i];
-            });
-            if (total > 0) {
-                const size_t at = h->locs_host.size();
-                h->locs_host.resize(at + (size_t)total);
-                par_memcpy(h->pool, h->locs_host.data() + at, s.h_locs, (size_t)total * sizeof(int));
-            }
+            if (s.dst_strand == s.h_strand) par_memcpy(h->pool, strand + s.first, s.h_strand, (size_t)cn);
+            if (s.dst_dist == s.h_dist) par_memcpy(h->pool, dist + s.first, s.h_dist, (size_t)cn * sizeof(int));
+            if (s.dst_locoff == s.h_locoff) par_memcpy(h->pool, loc_offsets + s.first, s.h_locoff, (size_t)cn * sizeof(long long));
         }
-        loc_base += total;
+        loc_total += total;
         s.busy = false;
         return SCT_OK;
     };
 
+    CUDA_TRY(cudaMemset(h->d_run, 0, sizeof(long long)));      // legacy stream: synchronous to the host, before any chunk
     int64_t first = 0, chunk = 0;
     while (first < n) {
         int64_t cn = std::min<int64_t>(h->chunk_reads, n - first);
@@ -357,9 +419,14 @@ int sct_align(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *rea
         const int si = (int)(chunk & 1);
         TRY(finish(si));
         ASlot &s = h->slot[si];
+        NvtxRange nv("sct_align: stage + enqueue chunk");
         TRY(stage_chunk(h, s, read_bytes, read_offsets, first, cn));
+        s.dst_strand = h->out_strand_pinned ? reinterpret_cast<signed char *>(strand) + first : s.h_strand;
+        s.dst_dist = h->out_dist_pinned ? dist + first : s.h_dist;
+        s.dst_locoff = h->out_locoff_pinned ? reinterpret_cast<long long *>(loc_offsets) + first : s.h_locoff;
         // kernels of this chunk behind pass 1 of the chunk in flight (two streams would otherwise run both side by side,
-        // finish together and leave the GPU idle during the host's un-staging); the H2D above still overlaps
+        // finish together and leave the GPU idle during the host's part; the running location base is advanced in chunk
+        // order); the H2D above still overlaps
         if (h->slot[1 - si].busy) CUDA_TRY(cudaStreamWaitEvent(s.stream, h->slot[1 - si].ev1, 0));
         TRY(enqueue_pass1(h, s));
         TRY(enqueue_fixed_copies(s));
@@ -371,9 +438,9 @@ int sct_align(sct_align_handle *h, const uint8_t *read_bytes, const int64_t *rea
     const int older = (int)(chunk & 1);
     TRY(finish(older));
     TRY(finish(1 - older));
-    loc_offsets[n] = loc_base;
-    *locs = h->locs_host.empty() ? nullptr : h->locs_host.data();
-    *n_locs = loc_base;
+    loc_offsets[n] = loc_total;
+    *locs = loc_total > 0 ? h->locs_pinned : nullptr;
+    *n_locs = loc_total;
     h->stats[5] = n;
     return SCT_OK;
 }
@@ -383,6 +450,11 @@ int sct_align_stage(sct_align_handle *h, const uint8_t *read_bytes, const int64_
     CUDA_TRY(cudaSetDevice(h->device));
     ASlot &s = h->slot[0];
     memset(h->stats, 0, sizeof h->stats);
+    {
+        const int64_t all_bytes = n > 0 ? read_offsets[n] - read_offsets[0] : 0;
+        h->in_bytes_pinned = all_bytes > 0 && is_pinned(read_bytes + read_offsets[0], (size_t)all_bytes);
+        h->in_off_pinned = n > 0 && is_pinned(read_offsets, (size_t)(n + 1) * sizeof(int64_t));
+    }
     TRY(stage_chunk(h, s, read_bytes, read_offsets, 0, n));
     CUDA_TRY(cudaStreamSynchronize(s.stream));
     h->staged = true;
@@ -395,9 +467,11 @@ int sct_align_run_staged(sct_align_handle *h, float *pass_ms, float *pass1_kerne
     CUDA_TRY(cudaSetDevice(h->device));
     ASlot &s = h->slot[0];
     h->stats[0] = 0;
+    CUDA_TRY(cudaMemsetAsync(h->d_run, 0, sizeof(long long), s.stream));
     TRY(enqueue_pass1(h, s));
     CUDA_TRY(cudaStreamSynchronize(s.stream));
-    TRY(enqueue_pass2(h, s, false));
+    if (*s.h_bad) return fail(SCT_E_ARG, "read_offsets must be non-decreasing (%u bad reads)", *s.h_bad);
+    TRY(enqueue_pass2(h, s, nullptr));
     CUDA_TRY(cudaStreamSynchronize(s.stream));
     float a = 0.f, b = 0.f;
     CUDA_TRY(cudaEventElapsedTime(&a, s.ev0, s.ev1));

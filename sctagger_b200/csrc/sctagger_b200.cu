@@ -423,22 +423,6 @@ int complete_pass(sct_handle *h, Slot &s) {
     return fail(SCT_E_STATE, "tie buffer did not converge");
 }
 
-// Is [p, p + bytes) page-locked host memory the copy engines can read / write directly?
-bool is_pinned(const void *p, size_t bytes) {
-    if (!p || bytes == 0) return false;
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
-        cudaGetLastError();
-        return false;
-    }
-    if (a.type != cudaMemoryTypeHost) return false;
-    if (cudaPointerGetAttributes(&a, (const char *)p + bytes - 1) != cudaSuccess) {
-        cudaGetLastError();
-        return false;
-    }
-    return a.type == cudaMemoryTypeHost;
-}
-
 // The library-owned pinned buffer holding the tie ids of the whole call grows geometrically and keeps its content.
 int ensure_ties(sct_handle *h, int64_t need, int64_t keep) {
     if (need <= h->ties_cap) return SCT_OK;

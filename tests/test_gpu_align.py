@@ -110,3 +110,25 @@ def test_align_errors():
             a.align(np.zeros(4, np.uint8), np.array([0, 3, 2], np.int64))
         with pytest.raises(_lib.SctError):
             a.run_staged()
+
+
+def test_page_locked_buffers_are_used_directly_and_bad_offsets_fail():
+    """sct_align copies from / to page-locked caller arrays without a staging pass: same result as with pageable arrays,
+    over several chunks; offsets that decrease fail the call (validated on the device)."""
+    rb, off = synth.make_reads(3000, 77)
+    with _lib.Aligner(synth.ADAPTER, threads=4, chunk_reads=700) as al:
+        want = al.align(rb, off)
+        prb, poff, out = _lib.Pinned.copy_of(rb), _lib.Pinned.copy_of(off), _lib.AlignBuffers(3000)
+        got = al.align(prb.array, poff.array, out=out, copy_locs=False)
+        assert al.stats()["chunks"] >= 4
+        for x, y in zip(got, want):
+            assert np.array_equal(x, y)
+        bad = off.copy()
+        bad[10] = bad[12] + 5
+        with pytest.raises(_lib.SctError):
+            al.align(rb, bad)
+        again = al.align(rb, off)                       # the handle stays usable
+        for x, y in zip(again, want):
+            assert np.array_equal(x, y)
+        for x in (prb, poff, out):
+            x.close()
