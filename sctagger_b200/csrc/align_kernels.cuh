@@ -22,7 +22,7 @@
 namespace sct {
 
 constexpr int ALN_THREADS = 128;
-constexpr int ALN_LONG_WORK = 384;        // pass 2: reads with more columns left than this get a warp instead of a thread
+constexpr int ALN_LONG_WORK = 160;        // pass 2: reads with more columns left than this get a warp instead of a thread
 constexpr int ALN_BUCKETS = 1024;        // length buckets of 32 bases; longer reads share the last bucket
 
 struct AlignParams {
@@ -38,7 +38,12 @@ struct AlignParams {
     int *dist;                           // -1 = NA
     int *n_locs;
     int2 *span;                          // first and last end position at the minimum of the winning adapter (pass 1 -> 2)
-    int *work;                           // columns pass 2 has to scan for the read (its sort key)
+    int *work;                           // columns pass 2 has to scan for the read
+    int *long_list;                      // reads whose span is long (work > ALN_LONG_WORK): one warp each in the count / emit kernels
+    unsigned int *n_long;
+    int *short_list;                     // reads with several end positions in a short span: one thread each, compacted
+    unsigned int *n_short;
+    int *long_cnt;                       // 32 per long read: end positions at the minimum in each lane's piece of the span
     const long long *loc_off;            // exclusive scan of n_locs (pass 2)
     int *locs;
     unsigned long long loc_cap;
@@ -81,30 +86,27 @@ __global__ void __launch_bounds__(ALN_BUCKETS) aln_bucket_scan_kernel(unsigned i
     hist[threadIdx.x] = sh[threadIdx.x] - v;
 }
 
-__global__ void __launch_bounds__(256) aln_scatter_kernel(const long long *__restrict__ off, int n, unsigned int *__restrict__ cursor,
-                                                          int *__restrict__ order) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const long long len = off[i + 1] - off[i];
-    order[atomicAdd(&cursor[len_bucket(len > 0 ? len : 0)], 1u)] = i;
-}
-
-// the same counting sort keyed by an int array (pass 2: columns each read still has to scan)
-__global__ void __launch_bounds__(256) aln_hist_work_kernel(const int *__restrict__ work, int n, unsigned int *__restrict__ hist) {
+// block-aggregated: ranks inside the block from shared-memory atomics, one global atomic per (block, bucket)
+__global__ void __launch_bounds__(1024) aln_scatter_kernel(const long long *__restrict__ off, int n, unsigned int *__restrict__ cursor,
+                                                           int *__restrict__ order) {
     __shared__ unsigned int sh[ALN_BUCKETS];
     for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x) sh[i] = 0;
     __syncthreads();
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) atomicAdd(&sh[len_bucket(work[i])], 1u);
-    __syncthreads();
-    for (int i = threadIdx.x; i < ALN_BUCKETS; i += blockDim.x)
-        if (sh[i]) atomicAdd(&hist[i], sh[i]);
-}
-
-__global__ void __launch_bounds__(256) aln_scatter_work_kernel(const int *__restrict__ work, int n, unsigned int *__restrict__ cursor,
-                                                               int *__restrict__ order) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    order[atomicAdd(&cursor[len_bucket(work[i])], 1u)] = i;
+    int b = 0;
+    unsigned int rank = 0;
+    if (i < n) {
+        const long long len = off[i + 1] - off[i];
+        b = len_bucket(len > 0 ? len : 0);
+        rank = atomicAdd(&sh[b], 1u);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < ALN_BUCKETS; k += blockDim.x) {
+        const unsigned int c = sh[k];
+        if (c) sh[k] = atomicAdd(&cursor[k], c);
+    }
+    __syncthreads();
+    if (i < n) order[sh[b] + rank] = i;
 }
 
 // extent of read r inside the chunk's byte buffer (clamped: bad offsets fail the call, they must not leave the buffer)
@@ -191,49 +193,152 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass1_kernel(const AlignParam
     if (best1 < best2) { s = '+'; d = best1; nl = c1; span = make_int2(f1, l1); }
     else if (best2 < best1) { s = '-'; d = best2; nl = c2; span = make_int2(f2, l2); }
     p.span[r] = span;
-    p.work[r] = nl ? (span.x > 2 * m + 2 ? 2 * m + 2 : span.x) + (span.y - span.x + 1) + (s == '-' ? nl * (m + d) : 0) : 0;
+    const int work = nl ? (span.x > 2 * m + 2 ? 2 * m + 2 : span.x) + (span.y - span.x + 1) + (s == '-' ? nl * (m + d) : 0) : 0;
+    p.work[r] = work;
+    if (work > ALN_LONG_WORK) p.long_list[atomicAdd(p.n_long, 1u)] = r;
+    else if (s != 0 && span.x != span.y) p.short_list[atomicAdd(p.n_short, 1u)] = r;
     p.strand[r] = s;
     p.dist[r] = d;
     p.n_locs[r] = nl;
 }
 
-// ---- pass 2 ---------------------------------------------------------------------------------------------------------
-// leftmost start s with Levenshtein(a2, read[s..e]) == d: reversed a2 against read[e], read[e-1], ... prefix-anchored
-__device__ __forceinline__ long long leftmost_start(const uint8_t *__restrict__ bytes, long long beg, long long e,
-                                                    const uint32_t *__restrict__ rpeq2, int m, int d) {
-    Myers q;
-    q.init(m);
-    const uint32_t top = 1u << (m - 1);
-    long long last = -1;
-    const long long avail = e - beg + 1;
-    const long long maxp = avail < (long long)m + d ? avail : (long long)m + d;
-    for (long long k = 0; k < maxp; ++k) {
-        q.step<true>(__ldg(rpeq2 + bytes[e - k]), top);
-        if (q.score == d) last = k;
+// ---- pass 1, packed keys (16 <= m <= 27) ---------------------------------------------------------------------------------
+// The bookkeeping of the kernel above costs as much as the recurrence: per adapter and column two compares and five
+// selects for (minimum, count, first, last).  Here the score is kept in units of U = 2^(m-1) — the weight of the top bit,
+// so score += (Ph & top) - (Mh & top) needs no shift — and two packed keys are folded with one add and one min each:
+//     score * U + (U - 1 - j)  ->  minimum score, LAST position at it;      score * U + j  ->  minimum score, FIRST position.
+// The number of end positions at the minimum is no longer counted here: a read whose first and last optimal end coincide
+// (nearly every read with an adapter) has one location; the others are counted by the count kernels over [first, last]
+// only.  Positions are relative to a segment of at most U - 1 columns; longer reads fold their segments (state carried).
+struct MyersU {                          // Myers column with the score in units of the top bit
+    uint32_t Pv, Mv, sk;
+    __device__ __forceinline__ void init(int m, uint32_t top) {
+        Pv = m >= 32 ? 0xFFFFFFFFu : ((1u << m) - 1u);
+        Mv = 0u;
+        sk = (uint32_t)m * top;
     }
-    return e - last;
-}
+    __device__ __forceinline__ void step(uint32_t Eq, uint32_t top) {
+        const uint32_t Xv = Eq | Mv;
+        const uint32_t Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
+        uint32_t Ph = Mv | ~(Xh | Pv);
+        uint32_t Mh = Pv & Xh;
+        sk = sk + (Ph & top) - (Mh & top);
+        Ph <<= 1;
+        Mh <<= 1;
+        Pv = Mh | ~(Xv | Ph);
+        Mv = Ph & Xv;
+    }
+};
 
-__global__ void __launch_bounds__(ALN_THREADS) aln_pass2_kernel(const AlignParams p) {
+__global__ void __launch_bounds__(ALN_THREADS) aln_pass1_fast_kernel(const AlignParams p) {
     __shared__ uint2 s_peq[256];
     for (int i = threadIdx.x; i < 256; i += ALN_THREADS) s_peq[i] = p.peq[i];
     __syncthreads();
     const int t = blockIdx.x * ALN_THREADS + threadIdx.x;
     if (t >= p.n) return;
     const int r = p.order[t];
-    const int nl = p.n_locs[r];
-    if (nl == 0 || p.work[r] > ALN_LONG_WORK) return;             // long spans: aln_pass2_long_kernel, one warp each
     long long beg, end;
     read_extent(p, r, beg, end);
-    const long long out0 = p.loc_off[r];
-    if ((unsigned long long)(out0 + nl) > p.loc_cap) return;      // the host grows the buffer and repeats the pass
+    const int m = p.m;
+    const uint32_t top = 1u << (m - 1), low = top - 1u;
+    MyersU a, b;
+    a.init(m, top);
+    b.init(m, top);
+    int best1 = m, best2 = m, f1 = 0, l1 = -1, f2 = 0, l2 = -1;      // HW scores never exceed m
+    bool any1 = false, any2 = false;
+    for (long long s0 = beg; s0 < end; s0 += (long long)low) {
+        const long long s1 = (s0 + (long long)low < end) ? s0 + (long long)low : end;
+        uint32_t j = 0, jr = low, kl1 = 0x7FFFFFFFu, kf1 = 0x7FFFFFFFu, kl2 = 0x7FFFFFFFu, kf2 = 0x7FFFFFFFu;
+        for_each_byte(p.bytes, s0, s1, [&](uint32_t ch, long long) {
+            const uint2 e = s_peq[ch];
+            a.step(e.x, top);
+            b.step(e.y, top);
+            kl1 = min(kl1, a.sk + jr);
+            kf1 = min(kf1, a.sk + j);
+            kl2 = min(kl2, b.sk + jr);
+            kf2 = min(kf2, b.sk + j);
+            ++j;
+            --jr;
+        });
+        const int base = (int)(s0 - beg);
+        const int sa = (int)(kl1 >> (m - 1)), sb = (int)(kl2 >> (m - 1));
+        if (sa < best1 || !any1) { best1 = sa; f1 = base + (int)(kf1 & low); l1 = base + (int)(low - (kl1 & low)); any1 = true; }
+        else if (sa == best1) l1 = base + (int)(low - (kl1 & low));
+        if (sb < best2 || !any2) { best2 = sb; f2 = base + (int)(kf2 & low); l2 = base + (int)(low - (kl2 & low)); any2 = true; }
+        else if (sb == best2) l2 = base + (int)(low - (kl2 & low));
+    }
+    // end == beg: edlib's empty target -> distance = query length for both adapters: a tie
+    signed char s = 0;
+    int d = -1;
+    int2 span = make_int2(0, -1);
+    if (best1 < best2) { s = '+'; d = best1; span = make_int2(f1, l1); }
+    else if (best2 < best1) { s = '-'; d = best2; span = make_int2(f2, l2); }
+    const int uniq = s != 0 && span.x == span.y;
+    const int work = s ? (span.x > 2 * m + 2 ? 2 * m + 2 : span.x) + (span.y - span.x + 1) + (s == '-' ? m + d : 0) : 0;
+    p.span[r] = span;
+    p.work[r] = work;
+    p.strand[r] = s;
+    p.dist[r] = d;
+    p.n_locs[r] = uniq;                                                // the others: count kernels
+    if (work > ALN_LONG_WORK) p.long_list[atomicAdd(p.n_long, 1u)] = r;
+    else if (s != 0 && !uniq) p.short_list[atomicAdd(p.n_short, 1u)] = r;
+}
+
+// ---- pass 2 ---------------------------------------------------------------------------------------------------------
+// leftmost start s with Levenshtein(a2, read[s..e]) == d: reversed a2 against read[e], read[e-1], ... prefix-anchored
+__device__ __noinline__ long long leftmost_start(const uint8_t *__restrict__ bytes, long long beg, long long e,
+                                                    const uint32_t *rpeq2 /* shared memory */, int m, int d) {
+    Myers q;
+    q.init(m);
+    const uint32_t top = 1u << (m - 1);
+    const long long avail = e - beg + 1;
+    const long long maxp = avail < (long long)m + d ? avail : (long long)m + d;
+    const long long lo = e - maxp + 1;                             // read[e], read[e-1], .. read[lo]
+    long long last_pos = e + 1;
+    // aligned 128-bit words, walked backwards (the buffer is padded and 16-byte aligned)
+    for (long long w = e & ~15ll; w + 15 >= lo; w -= 16) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(bytes + w));
+        const uint32_t qd[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 15; k >= 0; --k) {
+            const long long pos = w + k;
+            if (pos <= e && pos >= lo) {
+                q.step<true>(rpeq2[(qd[k >> 2] >> (8 * (k & 3))) & 0xFFu], top);
+                if (q.score == d) last_pos = pos;
+            }
+        }
+        if (w == 0) break;
+    }
+    return last_pos;
+}
+
+// Reads whose first and last optimal end differ, span short (the compacted short_list: full warps of similar work).
+// COUNT = true: the number of end positions at the minimum (n_locs); COUNT = false: the locations, behind the scan.
+template <bool COUNT>
+__global__ void __launch_bounds__(ALN_THREADS) aln_pass2_kernel(const AlignParams p) {
+    __shared__ uint2 s_peq[256];
+    __shared__ uint32_t s_rpeq2[256];
+    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) {
+        s_peq[i] = p.peq[i];
+        s_rpeq2[i] = p.rpeq2[i];
+    }
+    __syncthreads();
+    const unsigned int t = blockIdx.x * ALN_THREADS + threadIdx.x;
+    if (t >= *p.n_short) return;
+    const int r = p.short_list[t];                                // several end positions inside a short span
+    const signed char st = p.strand[r];
+    const int2 span = p.span[r];
+    const int nl = COUNT ? 0x7FFFFFFF : p.n_locs[r];
+    long long beg, end;
+    read_extent(p, r, beg, end);
+    const long long out0 = COUNT ? 0 : p.loc_off[r];
+    if (!COUNT && (unsigned long long)(out0 + nl) > p.loc_cap) return;      // the host grows the buffer and repeats the pass
     const int m = p.m, d = p.dist[r];
-    const bool fwd = p.strand[r] == '+';
+    const bool fwd = st == '+';
     const uint32_t top = 1u << (m - 1);
     // Every location lies in [first, last] (pass 1).  Row i of a semi-global DP column is <= i, so an optimal alignment
     // of any adapter prefix ends within 2m text characters of its start: an automaton restarted 2m + 2 characters before
     // `first` reproduces the exact columns from `first` on (and only over-estimates before it), and the scan stops at `last`.
-    const int2 span = p.span[r];
     const long long from = beg + (span.x > 2 * m + 2 ? span.x - (2 * m + 2) : 0), first = beg + span.x, to = beg + span.y + 1;
     Myers a;
     a.init(m);
@@ -242,68 +347,111 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass2_kernel(const AlignParam
         const uint2 e = s_peq[ch];
         a.step<false>(fwd ? e.x : e.y, top);
         if (a.score == d && k < nl && pos >= first) {
-            // '+': end position (scTagger.py:185);  '-': start - len(seq) - 1 (scTagger.py:189)
-            const long long v = fwd ? (pos - beg) : (leftmost_start(p.bytes, beg, pos, p.rpeq2, m, d) - beg) - (end - beg) - 1;
-            p.locs[out0 + k] = (int)v;
+            if (!COUNT) p.locs[out0 + k] = (int)(pos - beg);      // '+': the end position (scTagger.py:185)
             ++k;
         }
     });
+    if (COUNT) p.n_locs[r] = k;
+    // '-': start - len(seq) - 1 (scTagger.py:189).  Converted behind the scan so that the lanes of a warp walk their
+    // start searches together (inside the scan each lane would call it at a different column: one lane at a time)
+    if (!COUNT && !fwd)
+        for (int i = 0; i < k; ++i) {
+            const long long e = beg + p.locs[out0 + i];
+            p.locs[out0 + i] = (int)((leftmost_start(p.bytes, beg, e, s_rpeq2, m, d) - beg) - (end - beg) - 1);
+        }
+}
+
+// The reads with ONE location (first = last optimal end in pass 1 — nearly every read with an adapter): '+' is that end
+// position, '-' the leftmost start of the alignment ending there.
+__global__ void __launch_bounds__(ALN_THREADS) aln_emit_uniq_kernel(const AlignParams p) {
+    __shared__ uint32_t s_rpeq2[256];
+    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) s_rpeq2[i] = p.rpeq2[i];
+    __syncthreads();
+    const int t = blockIdx.x * ALN_THREADS + threadIdx.x;
+    if (t >= p.n) return;
+    const int r = p.order[t];
+    const signed char st = p.strand[r];
+    const int2 span = p.span[r];
+    if (st == 0 || span.x != span.y) return;
+    const long long out0 = p.loc_off[r];
+    if ((unsigned long long)(out0 + 1) > p.loc_cap) return;
+    long long beg, end;
+    read_extent(p, r, beg, end);
+    const long long pos = beg + span.x;
+    p.locs[out0] = (int)(st == '+' ? (pos - beg) : (leftmost_start(p.bytes, beg, pos, s_rpeq2, p.m, p.dist[r]) - beg) - (end - beg) - 1);
 }
 
 // Reads whose span is long (no adapter: equal minima scattered over the whole read) would each be one serial chain of
 // thousands of columns — the floor of the whole pass.  Here a warp takes one such read: every lane scans 1/32 of the span
 // behind its own 2m + 2 warm-up columns (same exactness argument), first counting its locations, then — after a warp
 // prefix sum of the counts — scanning again to write them in order.
+template <bool COUNT>
 __global__ void __launch_bounds__(ALN_THREADS) aln_pass2_long_kernel(const AlignParams p) {
     __shared__ uint2 s_peq[256];
-    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) s_peq[i] = p.peq[i];
+    __shared__ uint32_t s_rpeq2[256];
+    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) {
+        s_peq[i] = p.peq[i];
+        s_rpeq2[i] = p.rpeq2[i];
+    }
     __syncthreads();
-    const int w = (blockIdx.x * ALN_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (w >= p.n) return;
-    const int r = p.order[w];                                     // descending work: the long ones come first
-    const int nl = p.n_locs[r];
-    if (nl == 0 || p.work[r] <= ALN_LONG_WORK) return;
-    long long beg, end;
-    read_extent(p, r, beg, end);
-    const long long out0 = p.loc_off[r];
-    if ((unsigned long long)(out0 + nl) > p.loc_cap) return;
-    const int m = p.m, d = p.dist[r];
-    const bool fwd = p.strand[r] == '+';
-    const uint32_t top = 1u << (m - 1);
-    const int2 span = p.span[r];
-    const long long first = beg + span.x, stop = (beg + span.y + 1 < end) ? beg + span.y + 1 : end;
-    const long long piece = (stop - first + 31) / 32;
-    const long long lo = first + piece * lane, hi = (lo + piece < stop) ? lo + piece : stop;     // this lane emits [lo, hi)
-    const long long from = (lo - beg > 2 * m + 2) ? lo - (2 * m + 2) : beg;
-    int cnt = 0;
-    if (lo < hi) {
-        Myers a;
-        a.init(m);
-        for_each_byte(p.bytes, from, hi, [&](uint32_t ch, long long pos) {
-            const uint2 e = s_peq[ch];
-            a.step<false>(fwd ? e.x : e.y, top);
-            cnt += (a.score == d && pos >= lo);
-        });
-    }
-    int incl = cnt;
+    const int lane = threadIdx.x & 31;
+    const unsigned int n_long = *p.n_long;
+    for (unsigned int w = (blockIdx.x * ALN_THREADS + threadIdx.x) >> 5; w < n_long; w += (gridDim.x * ALN_THREADS) >> 5) {
+        const int r = p.long_list[w];
+        const int nl = COUNT ? 0x7FFFFFFF : p.n_locs[r];
+        long long beg, end;
+        read_extent(p, r, beg, end);
+        const long long out0 = COUNT ? 0 : p.loc_off[r];
+        if (!COUNT && (nl == 0 || (unsigned long long)(out0 + nl) > p.loc_cap)) continue;
+        const int m = p.m, d = p.dist[r];
+        const bool fwd = p.strand[r] == '+';
+        const uint32_t top = 1u << (m - 1);
+        const int2 span = p.span[r];
+        const long long first = beg + span.x, stop = (beg + span.y + 1 < end) ? beg + span.y + 1 : end;
+        const long long piece = (stop - first + 31) / 32;
+        const long long lo = first + piece * lane, hi = (lo + piece < stop) ? lo + piece : stop;     // this lane emits [lo, hi)
+        const long long from = (lo - beg > 2 * m + 2) ? lo - (2 * m + 2) : beg;
+        int cnt = 0;
+        if (!COUNT) {
+            cnt = p.long_cnt[(size_t)w * 32 + lane];              // counted by the COUNT launch
+        } else if (lo < hi) {
+            Myers a;
+            a.init(m);
+            for_each_byte(p.bytes, from, hi, [&](uint32_t ch, long long pos) {
+                const uint2 e = s_peq[ch];
+                a.step<false>(fwd ? e.x : e.y, top);
+                cnt += (a.score == d && pos >= lo);
+            });
+        }
+        if (COUNT) p.long_cnt[(size_t)w * 32 + lane] = cnt;
+        int incl = cnt;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= o) incl += v;
-    }
-    int k = incl - cnt;
-    if (cnt > 0) {
-        Myers a;
-        a.init(m);
-        for_each_byte(p.bytes, from, hi, [&](uint32_t ch, long long pos) {
-            const uint2 e = s_peq[ch];
-            a.step<false>(fwd ? e.x : e.y, top);
-            if (a.score == d && pos >= lo && k < nl) {
-                const long long v = fwd ? (pos - beg) : (leftmost_start(p.bytes, beg, pos, p.rpeq2, m, d) - beg) - (end - beg) - 1;
-                p.locs[out0 + k] = (int)v;
-                ++k;
-            }
-        });
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (COUNT) {
+            if (lane == 31) p.n_locs[r] = incl;
+            continue;
+        }
+        int k = incl - cnt;
+        if (cnt > 0) {
+            Myers a;
+            a.init(m);
+            for_each_byte(p.bytes, from, hi, [&](uint32_t ch, long long pos) {
+                const uint2 e = s_peq[ch];
+                a.step<false>(fwd ? e.x : e.y, top);
+                if (a.score == d && pos >= lo && k < nl) {
+                    p.locs[out0 + k] = (int)(pos - beg);
+                    ++k;
+                }
+            });
+            if (!fwd)                                              // converted behind the scan: see aln_pass2_kernel
+                for (int i = incl - cnt; i < k; ++i) {
+                    const long long e = beg + p.locs[out0 + i];
+                    p.locs[out0 + i] = (int)((leftmost_start(p.bytes, beg, e, s_rpeq2, m, d) - beg) - (end - beg) - 1);
+                }
+        }
     }
 }
 

@@ -22,7 +22,8 @@ struct ASlot {
     unsigned int *d_hist = nullptr;
     int *d_order = nullptr, *d_dist = nullptr, *d_nlocs = nullptr, *d_locs = nullptr;
     int2 *d_span = nullptr;
-    int *d_work = nullptr;
+    int *d_work = nullptr, *d_long = nullptr, *d_longcnt = nullptr, *d_short = nullptr;
+    unsigned int *d_nlong = nullptr;
     signed char *d_strand = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
@@ -38,7 +39,7 @@ struct ASlot {
 }  // namespace
 
 struct sct_align_handle {
-    int device = 0, m = 0, host_threads = 1;
+    int device = 0, m = 0, host_threads = 1, long_grid = 1184;
     uint2 *d_peq = nullptr;
     uint32_t *d_rpeq2 = nullptr;
     int64_t chunk_bytes = 0, chunk_reads = 0;
@@ -59,7 +60,7 @@ void free_aslot(ASlot &s) {
     host_free(s.h_dist); host_free(s.h_locs); host_free(s.h_bad);
     dev_free(s.d_bad); dev_free(s.d_locoff_out);
     dev_free(s.d_bytes); dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_bsums); dev_free(s.d_total);
-    dev_free(s.d_hist); dev_free(s.d_order); dev_free(s.d_dist); dev_free(s.d_nlocs); dev_free(s.d_locs); dev_free(s.d_span); dev_free(s.d_work);
+    dev_free(s.d_hist); dev_free(s.d_order); dev_free(s.d_dist); dev_free(s.d_nlocs); dev_free(s.d_locs); dev_free(s.d_span); dev_free(s.d_work); dev_free(s.d_long); dev_free(s.d_nlong); dev_free(s.d_longcnt); dev_free(s.d_short);
     dev_free(s.d_strand);
     s.cap_reads = s.cap_bytes = s.cap_locs = s.cap_hbytes = 0;
 }
@@ -85,13 +86,14 @@ int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes, bool stage_bytes) {
         CUDA_TRY(cudaMalloc(&s.d_total, 2 * sizeof(long long)));
         CUDA_TRY(cudaMallocHost(&s.h_bad, sizeof(unsigned int)));
         CUDA_TRY(cudaMalloc(&s.d_bad, sizeof(unsigned int)));
+        CUDA_TRY(cudaMalloc(&s.d_nlong, 2 * sizeof(unsigned int)));
         CUDA_TRY(cudaMalloc(&s.d_hist, ALN_BUCKETS * sizeof(unsigned int)));
     }
     if (reads > s.cap_reads) {
         const int64_t c = std::max<int64_t>(reads, 1024);
         host_free(s.h_off); host_free(s.h_locoff); host_free(s.h_strand); host_free(s.h_dist);
         dev_free(s.d_off); dev_free(s.d_locoff); dev_free(s.d_locoff_out); dev_free(s.d_bsums); dev_free(s.d_order); dev_free(s.d_dist);
-        dev_free(s.d_nlocs); dev_free(s.d_strand); dev_free(s.d_span); dev_free(s.d_work);
+        dev_free(s.d_nlocs); dev_free(s.d_strand); dev_free(s.d_span); dev_free(s.d_work); dev_free(s.d_long); dev_free(s.d_longcnt); dev_free(s.d_short);
         s.cap_reads = 0;
         CUDA_TRY(cudaMallocHost(&s.h_off, (size_t)(c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMallocHost(&s.h_locoff, (size_t)(c + 1) * sizeof(long long)));
@@ -106,6 +108,9 @@ int ensure_aslot(ASlot &s, int64_t reads, int64_t bytes, bool stage_bytes) {
         CUDA_TRY(cudaMalloc(&s.d_nlocs, (size_t)c * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_span, (size_t)c * sizeof(int2)));
         CUDA_TRY(cudaMalloc(&s.d_work, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_long, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_short, (size_t)c * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&s.d_longcnt, (size_t)c * 32 * sizeof(int)));
         CUDA_TRY(cudaMalloc(&s.d_strand, (size_t)c));
         s.cap_reads = c;
         TRY(ensure_locs(s, c * 2));
@@ -143,6 +148,11 @@ AlignParams make_aparams(sct_align_handle *h, ASlot &s) {
     p.n_locs = s.d_nlocs;
     p.span = s.d_span;
     p.work = s.d_work;
+    p.long_list = s.d_long;
+    p.n_long = s.d_nlong;
+    p.long_cnt = s.d_longcnt;
+    p.short_list = s.d_short;
+    p.n_short = s.d_nlong + 1;
     p.loc_off = s.d_locoff;
     p.locs = s.d_locs;
     p.loc_cap = (unsigned long long)s.cap_locs;
@@ -159,14 +169,20 @@ int enqueue_pass1(sct_align_handle *h, ASlot &s) {
         CUDA_TRY(cudaMemsetAsync(s.d_bad, 0, sizeof(unsigned int), s.stream));
         aln_hist_kernel<<<std::min((n + 255) / 256, 1184), 256, 0, s.stream>>>(s.d_off, n, s.b0, s.nbytes, s.d_hist, s.d_bad);
         aln_bucket_scan_kernel<<<1, ALN_BUCKETS, 0, s.stream>>>(s.d_hist);
-        aln_scatter_kernel<<<(n + 255) / 256, 256, 0, s.stream>>>(s.d_off, n, s.d_hist, s.d_order);
-        aln_pass1_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        aln_scatter_kernel<<<(n + 1023) / 1024, 1024, 0, s.stream>>>(s.d_off, n, s.d_hist, s.d_order);
+        CUDA_TRY(cudaMemsetAsync(s.d_nlong, 0, 2 * sizeof(unsigned int), s.stream));
+        // packed-key pass 1 where score * 2^(m-1) + position fits a word; it leaves the count of non-unique locations to
+        // the count kernels (which only scan [first, last] of those reads)
+        if (h->m >= 16 && h->m <= 27) aln_pass1_fast_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        else aln_pass1_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        aln_pass2_kernel<true><<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        aln_pass2_long_kernel<true><<<h->long_grid, ALN_THREADS, 0, s.stream>>>(p);
         const int nb = (n + 1023) / 1024;
         aln_block_sums_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums);
         aln_block_prefix_kernel<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total, h->d_run);
         aln_scan_apply_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums, s.d_locoff, s.d_locoff_out, s.d_total);
         CUDA_TRY(cudaGetLastError());
-        h->stats[0] += 7;
+        h->stats[0] += 9;
     } else {
         CUDA_TRY(cudaMemsetAsync(s.d_total, 0, 2 * sizeof(long long), s.stream));
         CUDA_TRY(cudaMemsetAsync(s.d_bad, 0, sizeof(unsigned int), s.stream));
@@ -194,16 +210,13 @@ int enqueue_pass2(sct_align_handle *h, ASlot &s, int32_t *copy_back /* where the
     if (total > 0) {
         const AlignParams p = make_aparams(h, s);
         const int n = (int)s.n;
-        // reads re-ordered by the columns pass 2 still has to scan (most: ~2m + a few; reads without the adapter: the
-        // whole read), so that the 32 reads of a warp finish together
-        CUDA_TRY(cudaMemsetAsync(s.d_hist, 0, ALN_BUCKETS * sizeof(unsigned int), s.stream));
-        aln_hist_work_kernel<<<std::min((n + 255) / 256, 1184), 256, 0, s.stream>>>(s.d_work, n, s.d_hist);
-        aln_bucket_scan_kernel<<<1, ALN_BUCKETS, 0, s.stream>>>(s.d_hist);
-        aln_scatter_work_kernel<<<(n + 255) / 256, 256, 0, s.stream>>>(s.d_work, n, s.d_hist, s.d_order);
-        aln_pass2_long_kernel<<<(n + (ALN_THREADS / 32) - 1) / (ALN_THREADS / 32), ALN_THREADS, 0, s.stream>>>(p);
-        aln_pass2_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        // reads with one location (nearly all) write it straight from pass 1's span; short spans are re-scanned by their
+        // thread, long ones (the list pass 1 built) by a warp each
+        aln_pass2_long_kernel<false><<<h->long_grid, ALN_THREADS, 0, s.stream>>>(p);
+        aln_pass2_kernel<false><<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        aln_emit_uniq_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
         CUDA_TRY(cudaGetLastError());
-        h->stats[0] += 5;
+        h->stats[0] += 3;
         if (copy_back != nullptr)
             CUDA_TRY(cudaMemcpyAsync(copy_back, s.d_locs, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
     }
@@ -271,6 +284,11 @@ int sct_align_create(int device, const uint8_t *adapter, int32_t adapter_length,
     if (!h) return fail(SCT_E_NOMEM, "out of host memory");
     h->device = device;
     h->m = adapter_length;
+    {
+        cudaDeviceProp prop;
+        CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+        h->long_grid = prop.multiProcessorCount * 8;
+    }
     h->host_threads = std::max(1, std::min({(int)threads, 8, (int)std::thread::hardware_concurrency() / std::max(1, ndev)}));
     h->pool = new (std::nothrow) HostPool(h->host_threads);
     // a1 = adapter, a2 = rev_compl(a1) (scTagger.py:363-365; identity on non-ACGT, scTagger.py:146-155)
