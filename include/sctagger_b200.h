@@ -88,23 +88,35 @@ int sct_run_staged(sct_handle *h, float *pass_ms, float *match_kernel_ms);
 int sct_fetch_staged(sct_handle *h, int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets,
                      const int32_t **tie_ids, int64_t *n_tie_ids);
 
-/* Counters of the last sct_match / sct_run_staged on this handle: [0] kernel launches, [1] segments on the
- * bit-parallel fast path, [2] segments on the generic path (non-ACGT bytes, > 32 bases, or tie-list overflow
- * re-runs), [3] host->device bytes, [4] device->host bytes, [5] chunks, [6] segments on the DP kernel, [7] (barcode, strand)
- * candidates the seeded kernel verified. */
+/* Counters of the last sct_match / sct_run_staged on this handle: [0] kernel launches, [1] segments on the one-window
+ * seeded (or tile) kernel: clean ACGT, <= 31 bases, [2] segments scored by the all-pairs generic kernel (tie-list
+ * overflow re-runs; every non-short segment when the barcodes cannot be seeded), [3] host->device bytes, [4] device->host
+ * bytes, [5] chunks, [6] segments on the DP kernel, [7] (barcode, strand) candidates the seeded kernels generated.
+ * Segments longer than 31 bases or with non-ACGT bytes run on the WINDOWED seeded kernel: sct_work_counters [4]. */
 int sct_stats(sct_handle *h, int64_t stats[8]);
 
 /*
  * Tuning / test hooks (set before the first sct_match / sct_stage):
  *   "chunk_segments", "chunk_bytes"       override the chunk sizing derived from mem_gb
  *   "tie_capacity_per_segment"            initial size of the device tie buffer (it grows and the pass is redone if short)
- *   "path"                                0 = automatic (seeded kernel for clean segments of <= 31 bases), 1 = force the
- *                                         generic bit-parallel kernel, 2 = force the DP kernel, 3 = use the all-pairs tile
+ *   "path"                                0 = automatic (seeded kernels: one window for clean segments of <= 31 bases,
+ *                                         overlapping windows for every other segment), 1 = force the generic
+ *                                         bit-parallel kernel, 2 = force the DP kernel, 3 = use the all-pairs tile
  *                                         kernel instead of the seeded one
  *   "stream_segments", "ramp_segments"    segments per streamed chunk of sct_match, and of its first chunk (the size
- *                                         doubles from chunk to chunk up to stream_segments so the pipeline fills fast)
+ *                                         quadruples from chunk to chunk up to stream_segments so the pipeline fills fast)
+ *   "chain_kernels"                       1 (default) = a chunk's kernels start behind the previous chunk's match kernel
  *   "seed_ctas_per_sm"                    resident CTAs per SM of the seeded kernel (grid = SMs x this)
- *   "seed_prefilter"                      0 = verify every seeded candidate in full (no anchored pre-check); same results
+ *   "seed_deepening"                      1 (default) = search error bounds 1, 2, .. max_error in turn and stop at the first
+ *                                         bound with a hit (only the minimum distance and its ties are reported);
+ *                                         0 = search max_error at once.  Same results.
+ *   "seed_prefilter"                      -1 (default) = anchored pre-check in the phases whose index buckets are dense
+ *                                         enough for it to pay, 1 = wherever possible, 0 = verify every candidate in full.
+ *                                         Same results.
+ *   "seed_direct"                         -1 (default) = phases with a sparse index probe and verify per lane, 0 = never,
+ *                                         1 = every phase.  Same results.
+ *   "seed_fast_max"                       longest clean segment of the one-window kernel (default 31; 0 sends every
+ *                                         segment through the windowed kernel — a test hook)
  */
 int sct_set_option(sct_handle *h, const char *key, int64_t value);
 
@@ -137,8 +149,10 @@ int sct_host_register(void *p, size_t bytes);
 int sct_host_unregister(void *p);
 
 /* Live work counters of the last sct_match / sct_run_staged (device-side, summed over the chunks): [0] index bucket
- * probes, [1] full automaton verifications (16 barcode characters each), [2] anchored pre-checks, [3] segments set up by
- * the seeded kernel, [4..7] reserved.  bench.py derives `roofline.useful` from these. */
+ * probes, [1] verifications, [2] anchored pre-checks, [3] phases run (windows x error bounds searched: with iterative
+ * deepening about 1.3 per segment on the bench input), [4] segments on the windowed seeded kernel (longer than 31 bases
+ * or with non-ACGT bytes), [5] LOP3 lane-operations of the automata (steps x (2k+1), k = error bound of the phase),
+ * [6..7] reserved.  bench.py derives `roofline.useful` from [5]. */
 int sct_work_counters(sct_handle *h, int64_t counters[8]);
 
 /* Name of the kernel that scores the clean segments with the handle's parameters and options (the dominant kernel of a
@@ -161,7 +175,10 @@ const char *sct_kernel_name(sct_handle *h);
  *                    '-': start - len(seq) - 1 for every location of a2 (scTagger.py:189), start = edlib's start of the
  *                         location = the leftmost start with the same distance for that end
  *                    locations of read r are (*locs)[loc_offsets[r] .. loc_offsets[r+1]); none for 'NA'
- *   Adapter length <= 32.  Host buffers in, host buffers out; *locs is library-owned until the next call / destroy.
+ *   Adapter length <= 32.  Host buffers in, host buffers out; *locs is library-owned (page-locked) until the next call /
+ *   destroy.  As with sct_match, arrays that lie in page-locked memory (sct_host_alloc / sct_host_register) are copied
+ *   from and to directly; pageable ones are staged by the handle's host threads.  read_offsets are validated on the
+ *   device (SCT_E_ARG when they decrease).
  */
 typedef struct sct_align_handle sct_align_handle;
 int sct_align_create(int device, const uint8_t *adapter, int32_t adapter_length, int32_t threads, double mem_gb,
