@@ -208,6 +208,36 @@ __device__ __forceinline__ bool seed_precheck(uint2 words, uint32_t aux, uint32_
     return (R[1] & full) != 0u;
 }
 
+// The K = 2 test of the two 5-mer pieces alone (neighbouring 5 characters within ONE edit): levels 0..1, 5 steps.  Used
+// for a block of 32 candidates whose slots all carry the level-1 flag — most blocks, since the candidate list is ordered by
+// (strand, piece, position) and the 5-mers own 90 % of it; a mixed block runs the general automaton above.
+__device__ __forceinline__ bool seed_precheck_l1x5(uint2 words, uint32_t aux, uint32_t pair_a, uint32_t full, uint32_t two,
+                                                   uint32_t init_a) {
+    const uint32_t w = ((aux & 64u) ? words.y : words.x) >> (aux & 63u);
+    const uint32_t tab_a = pair_a + (aux & 128u);
+    uint32_t R0, S0, R1, S1;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R0), "=r"(S0), "=r"(R1), "=r"(S1) : "r"(init_a + (aux >> 16)));
+    auto row = [&](uint32_t eq) {
+        const uint32_t r0 = S0 & eq;
+        const uint32_t s0 = mul_rt(r0, two);
+        const uint32_t t = R0 | S0 | s0;
+        const uint32_t r1 = (S1 & eq) | t;
+        R0 = r0;
+        S0 = s0;
+        R1 = r1;
+        S1 = mul_rt(r1, two);
+    };
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+        const uint32_t sh = m == 0 ? (w << 3) : (w >> (4 * m - 3));
+        uint32_t e0, e1;
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(e0), "=r"(e1) : "r"(and_or(sh, 0x78u, tab_a)));
+        row(e0);
+        if (m < 2) row(e1);
+    }
+    return (R1 & full) != 0u;
+}
+
 // Sort the warp's hit list ascending and drop duplicates (rank sort through a second buffer).  Returns the new count.
 __device__ __forceinline__ int sort_unique(uint32_t *list, uint32_t *tmp, int count, int lane) {
     if (count <= 1) return count;
@@ -545,7 +575,7 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
             __syncwarp();
         }
         const uint32_t full = (n >= 31) ? 0xFFFFFFFFu : ((1u << (n + 1)) - 1u);
-        uint32_t n_ver = 0;
+        uint32_t n_ver = 0, n_cheap = 0;
         // exact level of up to 32 queued candidates (lane < cnt), folded into the running (minimum, tie list)
         auto verify = [&](uint32_t item, bool valid) {
             int level = K + 1;
@@ -584,7 +614,11 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
             if (BL16 && PRE) {
                 if (pre_on) {
                     const uint2 words = __ldg(ix.ewords + entry);
-                    pass = seed_precheck<K>(words, aux, pair_a, full, ix.two, w.init_a) && pass;
+                    if (K == 2 && __all_sync(FULL, (aux & 512u) != 0u || !pass)) {
+                        pass = seed_precheck_l1x5(words, aux, pair_a, full, ix.two, w.init_a) && pass;
+                        n_cheap += min(32u, total - t0);
+                    } else
+                        pass = seed_precheck<K>(words, aux, pair_a, full, ix.two, w.init_a) && pass;
                 }
             }
             const unsigned pm = __ballot_sync(FULL, pass);
@@ -611,7 +645,8 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
             w.cnt[3] += 1ull;
             // automaton steps performed (x (2K+1) LOP3 each): full verifications + anchored pre-checks
             w.cnt[4] += (unsigned long long)((n_ver * (uint32_t)bl + 0u) * (uint32_t)(2 * K + 1)) +
-                        (pre_on ? (unsigned long long)total * (uint32_t)(seed_pre_steps(K) * (2 * seed_pre_levels(K) + 1)) : 0ull);
+                        (pre_on ? (unsigned long long)(total - n_cheap) * (uint32_t)(seed_pre_steps(K) * (2 * seed_pre_levels(K) + 1)) +
+                                      (unsigned long long)n_cheap * 15ull : 0ull);
             if (pre_on) w.cnt[5] += total;
         }
         __syncwarp();
