@@ -193,3 +193,21 @@ int sct_oracle_align_bv(const uint8_t *adapter, int m, const uint8_t *reads, con
                         int8_t *strand, int32_t *dist, int64_t *loc_off, int32_t **locs) {
     return align_impl(adapter, m, reads, off, n, workers, 1, strand, dist, loc_off, locs);
 }
+
+/* One query against one target, edlib.align(query, target, mode='HW', task='locations') restated: the distance and every
+ * (start, end) location at it — used to check the restatement against the vectors edlib publishes in its own README
+ * (tests/test_align_oracle.py).  starts / ends: caller-allocated, cap entries; returns the number of locations, the
+ * distance in *dist (-1 and 0 locations for an empty target... edlib: distance = query length, no location). */
+int sct_oracle_hw_locations(const uint8_t *q, int m, const uint8_t *t, int64_t n, int32_t *dist, int32_t *starts, int32_t *ends,
+                            int cap) {
+    ivec e = {0, 0, 0};
+    const int d = hw_dp(q, m, t, n, &e);
+    *dist = d;
+    int k = 0;
+    for (int64_t i = 0; i < e.n && k < cap; ++i, ++k) {
+        ends[k] = e.v[i];
+        starts[k] = (int32_t)leftmost_start(q, m, t, e.v[i], d);
+    }
+    free(e.v);
+    return k;
+}

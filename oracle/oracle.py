@@ -107,3 +107,21 @@ def align(adapter: bytes, read_bytes: np.ndarray, offsets: np.ndarray, workers: 
     locs = np.ctypeslib.as_array(ids, shape=(max(total, 1),))[:total].copy()
     L.sct_oracle_free(ids)
     return strand[:n], dist[:n], loc_off, locs
+
+
+def hw_locations(query: bytes, target: bytes, cap: int = 256):
+    """edlib.align(query, target, mode='HW', task='locations') as restated by oracle/align_oracle.c:
+    -> (editDistance, [(start, end), ...]).  Used to check the restatement against the vectors edlib publishes."""
+    L = lib()
+    fn = L.sct_oracle_hw_locations
+    u8p = ctypes.POINTER(ctypes.c_uint8)
+    i32p = ctypes.POINTER(ctypes.c_int32)
+    fn.restype = ctypes.c_int
+    fn.argtypes = [u8p, ctypes.c_int, u8p, ctypes.c_int64, i32p, i32p, i32p, ctypes.c_int]
+    q = np.frombuffer(bytes(query), dtype=np.uint8).copy()
+    t = np.frombuffer(bytes(target) or b"\0", dtype=np.uint8).copy()
+    d = ctypes.c_int32(0)
+    starts, ends = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+    k = fn(_ptr(q, ctypes.c_uint8), int(q.size), _ptr(t, ctypes.c_uint8), len(target), ctypes.byref(d),
+           _ptr(starts, ctypes.c_int32), _ptr(ends, ctypes.c_int32), cap)
+    return int(d.value), [(int(starts[i]), int(ends[i])) for i in range(k)]

@@ -161,3 +161,22 @@ def test_gpu_large_random_whitelist_against_numpy_twin():
     one = nh == 1
     assert one.sum() > 0.7 * n and np.array_equal(got_first[one], first[one])
     assert st["table_keys"] <= 2 * W and st["table_slots"] >= 4 * W and words
+
+
+def test_semantics_published_by_pyahocorasick():
+    """The example of pyahocorasick's own documentation: keys he / her / hers / she, values (insertion index, key),
+        for item in A.iter("_hershe_"): ...  ->  (2, (0, 'he')) (3, (1, 'her')) (4, (2, 'hers')) (6, (3, 'she')) (6, (0, 'he'))
+    — every occurrence is reported with its END index, overlapping ones and a key that is a suffix of another key included
+    (the order of two hits with the same end index is irrelevant to the stage, which only counts hits).  And the documented
+    dict-like add_word: a key added again keeps one entry and takes the new value (returns False)."""
+    from oracle import wl_oracle
+    A = wl_oracle.Automaton()
+    for idx, key in enumerate("he her hers she".split()):
+        assert A.add_word(key, (idx, key)) is True
+    A.make_automaton()
+    got = list(A.iter("_hershe_"))
+    assert sorted(got) == sorted([(2, (0, "he")), (3, (1, "her")), (4, (2, "hers")), (6, (3, "she")), (6, (0, "he"))])
+    assert [e for e, _ in got] == sorted(e for e, _ in got)
+    assert A.add_word("she", (9, "SHE")) is False
+    A.make_automaton()
+    assert (6, (9, "SHE")) in list(A.iter("_hershe_")) and (6, (3, "she")) not in list(A.iter("_hershe_"))
