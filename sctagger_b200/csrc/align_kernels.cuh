@@ -23,6 +23,7 @@ namespace sct {
 
 constexpr int ALN_THREADS = 128;
 constexpr int ALN_LONG_WORK = 160;        // pass 2: reads with more columns left than this get a warp instead of a thread
+constexpr int ALN_LONG_READ = 16384;      // pass 1: longer reads get a warp (aln_pass1_long_kernel) instead of a thread
 constexpr int ALN_BUCKETS = 1024;        // length buckets of 32 bases; longer reads share the last bucket
 
 struct AlignParams {
@@ -170,6 +171,7 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass1_kernel(const AlignParam
     const int r = p.order[t];
     long long beg, end;
     read_extent(p, r, beg, end);
+    if (end - beg > ALN_LONG_READ) return;                        // aln_pass1_long_kernel
     const int m = p.m;
     const uint32_t top = 1u << (m - 1);
     Myers a, b;
@@ -239,6 +241,7 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass1_fast_kernel(const Align
     const int r = p.order[t];
     long long beg, end;
     read_extent(p, r, beg, end);
+    if (end - beg > ALN_LONG_READ) return;                        // aln_pass1_long_kernel
     const int m = p.m;
     const uint32_t top = 1u << (m - 1), low = top - 1u;
     MyersU a, b;
@@ -282,6 +285,78 @@ __global__ void __launch_bounds__(ALN_THREADS) aln_pass1_fast_kernel(const Align
     p.n_locs[r] = uniq;                                                // the others: count kernels
     if (work > ALN_LONG_WORK) p.long_list[atomicAdd(p.n_long, 1u)] = r;
     else if (s != 0 && !uniq) p.short_list[atomicAdd(p.n_short, 1u)] = r;
+}
+
+// ---- pass 1 of very long reads: one warp per read ------------------------------------------------------------------------
+// One thread per read makes a pass as long as its longest read (a 100 kb nanopore read: 100 k serial columns).  Reads
+// longer than ALN_LONG_READ — the front of the length-sorted order — get a warp: lane l scans the l-th 1/32 of the read
+// behind 2m + 2 warm-up columns (row i of a semi-global DP column is <= i, so the columns from the piece's start on are
+// exact) and tracks (minimum, first, last) of its piece for both adapters; the warp folds them: minimum of the minima,
+// first optimal end from the lowest lane that has it, last from the highest.
+__global__ void __launch_bounds__(ALN_THREADS) aln_pass1_long_kernel(const AlignParams p) {
+    __shared__ uint2 s_peq[256];
+    for (int i = threadIdx.x; i < 256; i += ALN_THREADS) s_peq[i] = p.peq[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int m = p.m;
+    const uint32_t top = 1u << (m - 1);
+    for (int w = (blockIdx.x * ALN_THREADS + threadIdx.x) >> 5; w < p.n; w += (gridDim.x * ALN_THREADS) >> 5) {
+        const int r = p.order[w];
+        long long beg, end;
+        read_extent(p, r, beg, end);
+        if (end - beg <= ALN_LONG_READ) {
+            // the order is descending in len / 32 and every read of the open-ended last bucket is long: behind the first
+            // short read of a lower bucket there is no long one — but inside one bucket lengths are unordered, so only a
+            // read that could not share a bucket with a long one ends the scan
+            if (((end - beg) >> 5) < (ALN_LONG_READ >> 5)) break;
+            continue;
+        }
+        const long long piece = (end - beg + 31) / 32;
+        const long long lo = beg + piece * lane, hi = (lo + piece < end) ? lo + piece : end;
+        const long long from = (lo - beg > 2 * m + 2) ? lo - (2 * m + 2) : beg;
+        int b1 = 1 << 20, b2 = 1 << 20;
+        long long f1 = 0, l1 = -1, f2 = 0, l2 = -1;
+        if (lo < hi) {
+            Myers a, b;
+            a.init(m);
+            b.init(m);
+            for_each_byte(p.bytes, from, hi, [&](uint32_t ch, long long pos) {
+                const uint2 e = s_peq[ch];
+                a.step<false>(e.x, top);
+                b.step<false>(e.y, top);
+                if (pos >= lo) {
+                    if (a.score < b1) { b1 = a.score; f1 = pos; }
+                    if (a.score == b1) l1 = pos;
+                    if (b.score < b2) { b2 = b.score; f2 = pos; }
+                    if (b.score == b2) l2 = pos;
+                }
+            });
+        }
+        const int best1 = __reduce_min_sync(0xFFFFFFFFu, b1), best2 = __reduce_min_sync(0xFFFFFFFFu, b2);
+        const bool win1 = best1 < best2, win2 = best2 < best1;
+        signed char s = 0;
+        int d = -1;
+        int2 span = make_int2(0, -1);
+        if (win1 || win2) {
+            const unsigned has = __ballot_sync(0xFFFFFFFFu, (win1 ? b1 : b2) == (win1 ? best1 : best2));
+            const int lf = __ffs(has) - 1, ll = 31 - __clz(has);
+            const long long first = __shfl_sync(0xFFFFFFFFu, win1 ? f1 : f2, lf), last = __shfl_sync(0xFFFFFFFFu, win1 ? l1 : l2, ll);
+            s = win1 ? '+' : '-';
+            d = win1 ? best1 : best2;
+            span = make_int2((int)(first - beg), (int)(last - beg));
+        }
+        if (lane == 0) {
+            const int uniq = s != 0 && span.x == span.y;
+            const int work = s ? (span.x > 2 * m + 2 ? 2 * m + 2 : span.x) + (span.y - span.x + 1) + (s == '-' ? m + d : 0) : 0;
+            p.span[r] = span;
+            p.work[r] = work;
+            p.strand[r] = s;
+            p.dist[r] = d;
+            p.n_locs[r] = uniq;
+            if (work > ALN_LONG_WORK) p.long_list[atomicAdd(p.n_long, 1u)] = r;
+            else if (s != 0 && !uniq) p.short_list[atomicAdd(p.n_short, 1u)] = r;
+        }
+    }
 }
 
 // ---- pass 2 ---------------------------------------------------------------------------------------------------------

@@ -175,6 +175,7 @@ int enqueue_pass1(sct_align_handle *h, ASlot &s) {
         // the count kernels (which only scan [first, last] of those reads)
         if (h->m >= 16 && h->m <= 27) aln_pass1_fast_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
         else aln_pass1_kernel<<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
+        aln_pass1_long_kernel<<<h->long_grid, ALN_THREADS, 0, s.stream>>>(p);   // reads longer than ALN_LONG_READ: a warp each
         aln_pass2_kernel<true><<<(n + ALN_THREADS - 1) / ALN_THREADS, ALN_THREADS, 0, s.stream>>>(p);
         aln_pass2_long_kernel<true><<<h->long_grid, ALN_THREADS, 0, s.stream>>>(p);
         const int nb = (n + 1023) / 1024;
@@ -182,7 +183,7 @@ int enqueue_pass1(sct_align_handle *h, ASlot &s) {
         aln_block_prefix_kernel<<<1, 1024, 0, s.stream>>>(s.d_bsums, nb, s.d_total, h->d_run);
         aln_scan_apply_kernel<<<nb, 1024, 0, s.stream>>>(s.d_nlocs, n, s.d_bsums, s.d_locoff, s.d_locoff_out, s.d_total);
         CUDA_TRY(cudaGetLastError());
-        h->stats[0] += 9;
+        h->stats[0] += 10;
     } else {
         CUDA_TRY(cudaMemsetAsync(s.d_total, 0, 2 * sizeof(long long), s.stream));
         CUDA_TRY(cudaMemsetAsync(s.d_bad, 0, sizeof(unsigned int), s.stream));

@@ -97,6 +97,37 @@ def test_long_location_spans_take_the_warp_path():
     assert int(np.diff(got[2]).max()) > 300                                               # the homopolymer reads
 
 
+def test_very_long_reads_take_the_warp_per_read_pass1():
+    """Reads longer than 16 384 bases are scored by aln_pass1_long_kernel (lane l scans the l-th 1/32 of the read behind a
+    warm-up): adapters at piece seams, at both ends, on both strands, twice, not at all, lengths around the threshold and
+    around the length-bucket boundary, mixed with ordinary reads — against the oracle."""
+    rng = np.random.default_rng(33)
+    lut = np.frombuffer(b"ACGT", np.uint8)
+    a1 = synth.ADAPTER
+    rc = bytes({65: 84, 67: 71, 71: 67, 84: 65}[c] for c in reversed(a1))
+    rand = lambda n: lut[rng.integers(0, 4, n)].tobytes()
+
+    def plant(n, what, at):
+        b = bytearray(rand(n))
+        for w, a in zip(what, at):
+            b[a:a + len(w)] = w
+        return bytes(b)
+
+    reads = [rand(16384), rand(16385), rand(16415), rand(16416), rand(32735), rand(32736), rand(40000)]
+    for n in (20000, 50001, 120000):
+        piece = (n + 31) // 32
+        reads += [plant(n, [a1], [5]), plant(n, [rc], [n - 30]), plant(n, [a1], [piece * 7 - 11]),     # across a piece seam
+                  plant(n, [rc], [piece * 19 - 3]), plant(n, [a1, a1], [piece * 3, piece * 20 + 5]),    # twice, far apart
+                  plant(n, [a1[:-3]], [piece * 11 - 9]), plant(n, [rc, a1[:-2]], [100, n - 500])]
+    reads += [rand(int(rng.integers(200, 3000))) for _ in range(40)] + [plant(900, [a1], [33]), plant(900, [rc], [850])]
+    order = rng.permutation(len(reads))
+    reads = [reads[i] for i in order]
+    rb, off = _pack(reads)
+    want = oracle.align(a1, rb, off, workers=8, algo="bv")
+    _same(_lib.align_reads(a1, rb, off), want)
+    _same(_lib.align_reads(b"ACGTACGTACGTAAC", rb, off), oracle.align(b"ACGTACGTACGTAAC", rb, off, workers=8, algo="bv"))   # m = 15: generic pass 1
+
+
 def test_align_errors():
     with pytest.raises(_lib.SctError) as e:
         _lib.Aligner(b"A" * 33)
