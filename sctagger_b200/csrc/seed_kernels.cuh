@@ -1,26 +1,34 @@
-// SEEDED match kernel (sm_100a): pigeonhole seeds from a per-piece bucket index + exact bit-parallel verification.
-// Replaces, like match_fast_kernel, the reference's Trie.dfs / trie_search / merge (scTagger.py:566-599, 643-668,
-// 705-715) for clean ACGT segments of <= 31 bases, but scores only the (barcode, strand) pairs that can possibly be
-// within K edits instead of all 2B of them:
+// SEEDED match kernel (sm_100a): pigeonhole seeds from per-piece bucket indexes + exact bit-parallel verification,
+// error bounds searched in turn.  Replaces the reference's Trie.dfs / trie_search / merge (scTagger.py:566-599, 643-668,
+// 705-715) for every segment — clean ACGT segments of <= 31 bases as one window, longer ones and those with non-ACGT
+// bytes as overlapping windows — but scores only the (barcode, strand) pairs that can possibly be within k edits instead
+// of all 2B of them:
 //
-//   * The barcode is cut into K+1 disjoint pieces.  K edits destroy at most K pieces, so a barcode within K edits of a
+//   * ITERATIVE DEEPENING: phase k = 1, 2, .. max_error looks for every barcode within k edits and the search stops at the
+//     first phase that finds one — the reference reports only the minimum distance and the barcodes tied at it, and phase
+//     k is complete for every distance <= k (match_seed_kernel below).
+//   * The barcode is cut into k+1 disjoint pieces.  k edits destroy at most k pieces, so a barcode within k edits of a
 //     substring of the segment T has a piece occurring EXACTLY in T, at a text position j with
-//     o_p - K <= j <= n - (bl - o_p) + K.  Every piece has a bucket table (bucket = 2-bit code of the piece) built once
-//     in sct_create; a segment's candidates are therefore 2 strands x (K+1) pieces x <= 32 positions bucket ranges.
-//   * One warp owns one segment.  The ranges' lengths are prefix-summed (warp scan) into a per-warp slot table in shared
-//     memory; the flattened candidate list is then walked 32 candidates at a time, each lane finding its slot by binary
-//     search (load-balanced expansion: no lane idles on a short bucket).
-//   * Each candidate is scored exactly by a k-error Shift-And automaton with the roles swapped: the state vector runs
-//     over the positions of T (one 32-bit register), one barcode character is consumed per step, and Eq[c] — which
-//     positions of T hold character c — is warp-uniform per strand (8 words of shared memory per warp):
+//     o_p - k <= j <= n - (bl - o_p) + k.  Every piece has a bucket table (bucket = 2-bit code of the piece) built once
+//     per error bound in sct_create; a window's candidates are 2 strands x (k+1) pieces x <= 32 positions bucket ranges.
+//   * One warp owns one segment.  Dense phases (seed_phase): the ranges' lengths are prefix-summed (warp scan) into a
+//     per-warp slot table in shared memory and the flattened candidate list is walked 32 candidates at a time (no lane
+//     idles on a short bucket); an anchored pre-check of the RESPONSIBLE seed (seed_precheck) discards most candidates
+//     after a few automaton steps.  Sparse phases (seed_phase_direct): every lane probes one bucket and verifies its
+//     entries directly.
+//   * Each surviving candidate is scored exactly by a k-error Shift-And automaton with the roles swapped: the state vector
+//     runs over the positions of T (one 32-bit register per level), one barcode character is consumed per step, and Eq[c] —
+//     which positions of T hold character c — is warp-uniform per strand (pair tables in shared memory):
 //         R0' = (R0 << 1) & Eq[c]
 //         Rd' = ((Rd << 1) & Eq[c]) | R_{d-1} | (R_{d-1} << 1) | (R'_{d-1} << 1)         match | delete | subst | insert
-//     start R_d = all positions (free start in T); after bl steps the barcode is within d edits iff R_d & mask(n+1) != 0.
+//     start R_d = all positions (free start in T; the window's slice of the -t prefix rule's start states for segments with
+//     non-ACGT bytes); after bl steps the barcode is within d edits iff R_d & mask(n+1) != 0.
 //     The shifts are IMADs by a run-time 2 (FMA pipe), so the ALU pipe only sees the LOP3s and the character extract.
 //   * Reverse strand: d(revcomp(P), T) = d(P, revcomp(T)): revcomp(T) is scored against the same forward barcodes.
 //   * Hits (rare) are folded into the warp's (minimum, tie list); the list is sorted and de-duplicated at the end (a
-//     barcode is found once per surviving piece) so tie ids come out ascending = the reference's sorted((bid, strand)).
-// tests/index_model.py is the Python twin of this file.
+//     barcode is found once per surviving piece and window) so tie ids come out ascending = the reference's
+//     sorted((bid, strand)).
+// tests/index_model.py is the Python twin of this file (one-window and windowed variants).
 #pragma once
 #include "match_kernels.cuh"
 
