@@ -78,6 +78,7 @@ struct sct_handle {
     size_t fast_smem = 0;
     int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
     int64_t stream_segs = 0;                    // segments per streamed chunk of sct_match (<= chunk_segs)
+    int64_t tail_segs = 1 << 16;                // size of the last streamed chunk (option tail_segments)
     int64_t ramp_segs = 1 << 15;                // size of the first streamed chunk (doubles up to stream_segs)
     int host_threads = 1;        // worker threads for staging / un-staging (from -t, capped)
     HostPool *pool = nullptr;
@@ -770,6 +771,9 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "ramp_segments") {
         if (value < 1) return fail(SCT_E_ARG, "ramp_segments must be >= 1");
         h->ramp_segs = value;
+    } else if (k == "tail_segments") {
+        if (value < 0) return fail(SCT_E_ARG, "tail_segments must be >= 0");
+        h->tail_segs = value;
     } else if (k == "stream_segments") {
         if (value < 1) return fail(SCT_E_ARG, "stream_segments must be >= 1");
         h->stream_segs = std::min<int64_t>(value, h->chunk_segs);
@@ -862,6 +866,9 @@ static int match_impl(sct_handle *h, const uint8_t *seg_bytes, const int64_t *se
     int64_t ramp = std::min<int64_t>(h->stream_segs, h->ramp_segs);
     while (first < n) {
         int64_t cn = std::min<int64_t>(std::min(h->stream_segs, ramp), n - first);
+        // the call ends with a SMALL chunk: what follows the last kernel — its result copies, the tie copy, two host
+        // synchronisations — is exposed, and it is proportional to the last chunk
+        if (cn == n - first && cn > 2 * h->tail_segs) cn -= h->tail_segs;
         ramp = std::min<int64_t>(h->stream_segs, ramp * 4);   // 32 k, 128 k, 512 k, then full chunks: every chunk costs ~70 us of kernel tail + launch gaps
         const int64_t limit = seg_offsets[first] + h->chunk_bytes;
         if (seg_offsets[first + cn] > limit) {

@@ -14,8 +14,8 @@ for n in (10_000_000, 1_250_000):
         m.stage(sb, off)
         m.run_staged()
         res = min(m.run_staged()[0] for _ in range(3))
-    for stream, ramp, chain in ((1 << 19, 1 << 15, 1), (1 << 19, 1 << 15, 0), (1 << 20, 1 << 15, 1), (1 << 20, 1 << 15, 0), (1 << 18, 1 << 15, 0), (1 << 20, 1 << 17, 0), (1 << 20, 1 << 17, 1)):
-        with _lib.Matcher(bc, mr, 16, stream_segments=stream, ramp_segments=ramp, chain_kernels=chain) as m:
+    for stream, ramp, chain in ((1 << 20, 1 << 15, 0), (1 << 20, 1 << 15, 1 << 14), (1 << 20, 1 << 15, 1 << 15), (1 << 20, 1 << 15, 1 << 16), (1 << 20, 1 << 15, 1 << 17), (1 << 20, 1 << 18, 1 << 16)):
+        with _lib.Matcher(bc, mr, 16, stream_segments=stream, ramp_segments=ramp, tail_segments=chain) as m:
             for _ in range(2):
                 m.match(psb.array, poff.array, out=out, copy_ties=False)
             ts = []
@@ -23,7 +23,7 @@ for n in (10_000_000, 1_250_000):
                 t0 = time.perf_counter()
                 m.match(psb.array, poff.array, out=out, copy_ties=False)
                 ts.append(time.perf_counter() - t0)
-            print(json.dumps({"n": n, "resident_ms": round(res, 3), "stream": stream, "ramp": ramp, "chain": chain, "chunks": m.stats()["chunks"],
+            print(json.dumps({"n": n, "resident_ms": round(res, 3), "stream": stream, "ramp": ramp, "tail": chain, "chunks": m.stats()["chunks"],
                               "e2e_ms_min": round(1e3 * min(ts), 3), "e2e_ms_med": round(1e3 * sorted(ts)[3], 3)}), flush=True)
     for x in (psb, poff, out):
         x.close()
