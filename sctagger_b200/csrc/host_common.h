@@ -27,7 +27,7 @@ inline thread_local std::string g_err;
 // SCT_TRACE=1: per-call host-side phase times of sct_match on stderr (staging / waiting on the GPU / un-staging)
 struct Trace {
     bool on = getenv("SCT_TRACE") != nullptr;
-    double t_stage = 0, t_wait = 0, t_fetch = 0, t_check = 0;
+    double t_stage = 0, t_wait = 0, t_fetch = 0, t_check = 0, t_alloc = 0;
     static double now() {
         return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
     }

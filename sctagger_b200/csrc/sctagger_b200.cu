@@ -22,6 +22,7 @@ constexpr int N_SLOTS = 3;
 
 struct Slot {
     int64_t cap_segs = 0, cap_bytes = 0;
+    int64_t hcap_segs = 0, hcap_bytes = 0;   // pinned staging (allocated only for pageable caller arrays)
     unsigned long long tie_cap = 0;
     // pinned host staging
     uint8_t *h_bytes = nullptr;
@@ -78,6 +79,7 @@ struct sct_handle {
     size_t fast_smem = 0;
     int64_t chunk_segs = 0, chunk_bytes = 0;   // capacity of one slot (sct_stage batch limit), from -m
     int64_t stream_segs = 0;                    // segments per streamed chunk of sct_match (<= chunk_segs)
+    int64_t stream_segs_pageable = 1 << 20;     // ... when a caller array is pageable (staged through pinned buffers)
     int64_t tail_segs = 1 << 16;                // size of the last streamed chunk (option tail_segments)
     int64_t ramp_segs = 1 << 15;                // size of the first streamed chunk (doubles up to stream_segs)
     int host_threads = 1;        // worker threads for staging / un-staging (from -t, capped)
@@ -93,6 +95,8 @@ struct sct_handle {
     Slot slot[N_SLOTS];
     int32_t *ties_pinned = nullptr;             // tie ids of the whole call (library-owned, pinned; sct_match's *tie_ids)
     int64_t ties_cap = 0;
+    int64_t slot_segs_hint = 0, slot_bytes_hint = 0;   // full-chunk size of the call in progress
+    int64_t call_segments = 0;                  // n of the sct_match call in progress
     long long *d_tie_run = nullptr;             // device-side running sum of ties over the chunks of one call
     // which of the caller's arrays are page-locked (cudaHostAlloc / cudaHostRegister / sct_host_alloc): those are
     // copied from / to directly, without the staging pass through the slot's pinned buffers
@@ -113,7 +117,7 @@ int free_slot(Slot &s) {
     s.pk_words = 0;
     dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart); dev_free(s.d_tiebuf); dev_free(s.d_tieout);
     dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_total);
-    s.cap_segs = s.cap_bytes = 0;
+    s.cap_segs = s.cap_bytes = s.hcap_segs = s.hcap_bytes = 0;
     s.tie_cap = 0;
     return SCT_OK;
 }
@@ -149,15 +153,10 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
     }
     if (segs > s.cap_segs) {
         const int64_t c = std::max<int64_t>(segs, 1024);
-        host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
         dev_free(s.d_rec); dev_free(s.d_segflag); dev_free(s.d_off); dev_free(s.d_fast); dev_free(s.d_gen);
         dev_free(s.d_ovf); dev_free(s.d_dp); dev_free(s.d_min); dev_free(s.d_nt); dev_free(s.d_tstart);
         dev_free(s.d_toff); dev_free(s.d_bsums); dev_free(s.d_wide);
         s.cap_segs = 0;
-        CUDA_TRY(cudaMallocHost(&s.h_off, (c + 1) * sizeof(long long)));
-        CUDA_TRY(cudaMallocHost(&s.h_min, c * sizeof(int)));
-        CUDA_TRY(cudaMallocHost(&s.h_nt, c * sizeof(int)));
-        CUDA_TRY(cudaMallocHost(&s.h_toff, (c + 1) * sizeof(long long)));
         CUDA_TRY(cudaMalloc(&s.d_rec, (size_t)c * REC_BYTES));
         CUDA_TRY(cudaMalloc(&s.d_segflag, (size_t)c));
         CUDA_TRY(cudaMalloc(&s.d_off, (c + 1) * sizeof(long long)));
@@ -177,14 +176,32 @@ int ensure_slot(sct_handle *h, Slot &s, int64_t segs, int64_t bytes) {
     }
     if (bytes > s.cap_bytes) {
         const int64_t c = std::max<int64_t>(bytes, 4096);
-        host_free(s.h_bytes);
         dev_free(s.d_bytes);
         dev_free(s.d_colinfo);
         s.cap_bytes = 0;
-        CUDA_TRY(cudaMallocHost(&s.h_bytes, (size_t)c + 64));
         CUDA_TRY(cudaMalloc(&s.d_bytes, (size_t)c + 64));
         CUDA_TRY(cudaMalloc(&s.d_colinfo, (size_t)c + 64));
         s.cap_bytes = c;
+    }
+    // pinned staging for the caller's pageable arrays only (page-locking costs ~1 ms per MB: a fresh handle that is fed
+    // page-locked arrays allocates none of it)
+    const bool need_h = !(h->in_off_pinned && h->out_min_pinned && h->out_nt_pinned && h->out_toff_pinned);
+    if (need_h && segs > s.hcap_segs) {
+        const int64_t c = std::max<int64_t>(segs, 1024);
+        host_free(s.h_off); host_free(s.h_min); host_free(s.h_nt); host_free(s.h_toff);
+        s.hcap_segs = 0;
+        CUDA_TRY(cudaMallocHost(&s.h_off, (c + 1) * sizeof(long long)));
+        CUDA_TRY(cudaMallocHost(&s.h_min, c * sizeof(int)));
+        CUDA_TRY(cudaMallocHost(&s.h_nt, c * sizeof(int)));
+        CUDA_TRY(cudaMallocHost(&s.h_toff, (c + 1) * sizeof(long long)));
+        s.hcap_segs = c;
+    }
+    if (!h->in_bytes_pinned && bytes > s.hcap_bytes) {
+        const int64_t c = std::max<int64_t>(bytes, 4096);
+        host_free(s.h_bytes);
+        s.hcap_bytes = 0;
+        CUDA_TRY(cudaMallocHost(&s.h_bytes, (size_t)c + 64));
+        s.hcap_bytes = c;
     }
     // 2-bit packed text of the seeded mode: segment i starts at word (byte offset >> 5) + i
     const int64_t pkw = s.cap_bytes / 32 + s.cap_segs + 4;
@@ -446,7 +463,11 @@ int start_chunk(sct_handle *h, Slot &s, Slot *prev, const uint8_t *seg_bytes, co
                 int32_t *min_ed, int32_t *n_ties, int64_t *tie_offsets) {
     const int64_t b0 = off[first], nbytes = off[first + n] - b0;
     if (nbytes < 0) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing (chunk starting at segment %lld)", (long long)first);
-    TRY(ensure_slot(h, s, n, nbytes));
+    const double ta = Trace::now();
+    // a slot is allocated once, at the size of the call's full chunks (the ramp's small chunks would otherwise size it
+    // first and every slot would be freed and allocated again two chunks later: 0.2 s on a fresh handle)
+    TRY(ensure_slot(h, s, std::max<int64_t>(n, h->slot_segs_hint), std::max<int64_t>(nbytes, h->slot_bytes_hint)));
+    g_tr.t_alloc += Trace::now() - ta;
     const double t0 = Trace::now();
     const uint8_t *src_bytes = seg_bytes + b0;
     const long long *src_off = reinterpret_cast<const long long *>(off + first);
@@ -487,7 +508,14 @@ int fetch_results(sct_handle *h, Slot &s, int32_t *min_ed, int32_t *n_ties, int6
     if (n > 0) {
         if (!s.copies_enqueued) TRY(enqueue_result_copies(s));
         if (total > 0) {
-            TRY(ensure_ties(h, base + total, base));
+            // grow once, to the size the call will need if the rest of the segments tie like the ones seen so far
+            // (page-locking ~1 ms per MB: doubling from 64 k entries up cost a fresh handle 0.2 s on 10 M segments)
+            int64_t want = base + total;
+            if (want > h->ties_cap && h->call_segments > 0 && s.first + n > 0)
+                want = std::max<int64_t>(want, (int64_t)(1.25 * (double)(base + total) / (double)(s.first + n) * (double)h->call_segments));
+            const double ta = Trace::now();
+            TRY(ensure_ties(h, want, base));
+            g_tr.t_alloc += Trace::now() - ta;
             CUDA_TRY(cudaMemcpyAsync(h->ties_pinned + base, s.d_tieout, (size_t)total * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
         }
         double t0 = Trace::now();
@@ -744,6 +772,7 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
         if (value < 1) return fail(SCT_E_ARG, "chunk_segments must be >= 1");
         h->chunk_segs = value;
         h->stream_segs = value;
+        h->stream_segs_pageable = value;
         h->ramp_segs = value;
         h->chunk_bytes = std::max<int64_t>(h->chunk_bytes, 64);
     } else if (k == "chunk_bytes") {
@@ -777,6 +806,7 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "stream_segments") {
         if (value < 1) return fail(SCT_E_ARG, "stream_segments must be >= 1");
         h->stream_segs = std::min<int64_t>(value, h->chunk_segs);
+        h->stream_segs_pageable = h->stream_segs;
     } else if (k == "seed_fast_max") {   // test hook: 0 routes every segment through the windowed variant
         if (value < 0 || value > SEED_MAX_LEN) return fail(SCT_E_ARG, "seed_fast_max must be 0..%d", SEED_MAX_LEN);
         h->seed_fast_max = (int)value;
@@ -831,11 +861,12 @@ static int match_impl(sct_handle *h, const uint8_t *seg_bytes, const int64_t *se
         return fail(SCT_E_ARG, "NULL argument");
     if (n > 0 && !seg_bytes && seg_offsets[n] > seg_offsets[0]) return fail(SCT_E_ARG, "seg_bytes is NULL");
     const double t_begin = Trace::now();
-    g_tr.t_stage = g_tr.t_wait = g_tr.t_fetch = 0;
+    g_tr.t_stage = g_tr.t_wait = g_tr.t_fetch = g_tr.t_alloc = 0;
     CUDA_TRY(cudaSetDevice(h->device));
     memset(h->stats, 0, sizeof h->stats);
     memset(h->work, 0, sizeof h->work);
     h->staged = h->staged_ran = false;
+    h->call_segments = n;
     // page-locked caller arrays (sct_host_alloc / sct_host_register / cudaHostAlloc) are copied from and to directly
     const int64_t all_bytes = n > 0 ? seg_offsets[n] - seg_offsets[0] : 0;
     h->in_bytes_pinned = n > 0 && all_bytes > 0 && is_pinned(seg_bytes + seg_offsets[0], (size_t)all_bytes);
@@ -863,13 +894,20 @@ static int match_impl(sct_handle *h, const uint8_t *seg_bytes, const int64_t *se
         CUDA_TRY(cudaMemsetAsync(h->d_tie_run, 0, sizeof(long long), h->slot[0].stream));   // chunk 0 runs on this stream
     }
     // the first chunks are small so that the first kernel starts (and the pipeline fills) after a short copy
-    int64_t ramp = std::min<int64_t>(h->stream_segs, h->ramp_segs);
+    // pageable caller arrays go through pinned staging buffers, whose allocation (page-locking, ~1 ms per MB, three slots)
+    // a fresh handle pays in its first call: smaller chunks there (a chunk costs ~70 us, the staging of a 1 Mi-segment
+    // chunk ~60 ms of allocation)
+    const bool all_pinned = h->in_bytes_pinned && h->in_off_pinned && h->out_min_pinned && h->out_nt_pinned && h->out_toff_pinned;
+    const int64_t stream_segs = all_pinned ? h->stream_segs : std::min<int64_t>(h->stream_segs, h->stream_segs_pageable);
+    int64_t ramp = std::min<int64_t>(stream_segs, h->ramp_segs);
+    h->slot_segs_hint = std::min<int64_t>(stream_segs, n);
+    h->slot_bytes_hint = n > 0 ? std::min<int64_t>(h->chunk_bytes, (int64_t)(1.1 * (double)all_bytes / (double)n * (double)h->slot_segs_hint) + 4096) : 0;
     while (first < n) {
-        int64_t cn = std::min<int64_t>(std::min(h->stream_segs, ramp), n - first);
+        int64_t cn = std::min<int64_t>(std::min(stream_segs, ramp), n - first);
         // the call ends with a SMALL chunk: what follows the last kernel — its result copies, the tie copy, two host
         // synchronisations — is exposed, and it is proportional to the last chunk
         if (cn == n - first && cn > 2 * h->tail_segs) cn -= h->tail_segs;
-        ramp = std::min<int64_t>(h->stream_segs, ramp * 4);   // 32 k, 128 k, 512 k, then full chunks: every chunk costs ~70 us of kernel tail + launch gaps
+        ramp = std::min<int64_t>(stream_segs, ramp * 4);   // 32 k, 128 k, 512 k, then full chunks: every chunk costs ~70 us of kernel tail + launch gaps
         const int64_t limit = seg_offsets[first] + h->chunk_bytes;
         if (seg_offsets[first + cn] > limit) {
             const int64_t *e = std::upper_bound(seg_offsets + first, seg_offsets + first + cn + 1, limit);
@@ -891,8 +929,8 @@ static int match_impl(sct_handle *h, const uint8_t *seg_bytes, const int64_t *se
     *tie_ids = tie_total > 0 ? h->ties_pinned : nullptr;
     *n_tie_ids = tie_total;
     if (g_tr.on)
-        fprintf(stderr, "[sct_match] n=%lld chunks=%lld total %.3f ms: check %.3f stage %.3f wait %.3f fetch %.3f pinned in %d%d out %d%d%d\n",
-                (long long)n, (long long)chunk, 1e3 * (Trace::now() - t_begin), 1e3 * g_tr.t_check, 1e3 * g_tr.t_stage,
+        fprintf(stderr, "[sct_match] n=%lld chunks=%lld total %.3f ms: check %.3f alloc %.3f stage %.3f wait %.3f fetch %.3f pinned in %d%d out %d%d%d\n",
+                (long long)n, (long long)chunk, 1e3 * (Trace::now() - t_begin), 1e3 * g_tr.t_check, 1e3 * g_tr.t_alloc, 1e3 * g_tr.t_stage,
                 1e3 * g_tr.t_wait, 1e3 * g_tr.t_fetch, h->in_bytes_pinned, h->in_off_pinned, h->out_min_pinned,
                 h->out_nt_pinned, h->out_toff_pinned);
     return SCT_OK;
@@ -907,6 +945,8 @@ int sct_stage(sct_handle *h, const uint8_t *seg_bytes, const int64_t *seg_offset
     if (nbytes < 0) return fail(SCT_E_ARG, "seg_offsets must be non-decreasing");
     // the resident batch may be larger than a streamed chunk (bench.py keeps a whole 10 M-segment shard in HBM): it only
     // has to fit the device, which cudaMalloc decides
+    // the resident batch is copied straight from / to the caller's arrays: no pinned staging
+    h->in_bytes_pinned = h->in_off_pinned = h->out_min_pinned = h->out_nt_pinned = h->out_toff_pinned = true;
     TRY(ensure_slot(h, s, n, nbytes));
     const int64_t b0 = seg_offsets[0];
     if (nbytes > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, seg_bytes + b0, (size_t)nbytes, cudaMemcpyHostToDevice, s.stream));
