@@ -194,6 +194,21 @@ int sct_align_run_staged(sct_align_handle *h, float *pass_ms, float *pass1_kerne
 int sct_align_stats(sct_align_handle *h, int64_t stats[8]);
 int sct_align_set_option(sct_align_handle *h, const char *key, int64_t value);
 
+/*
+ * Allocation-free variant of pass 1 of the adapter alignment: strand[r] ('+', '-', 0 = NA) and dist[r] (-1 = NA) of every
+ * read, exactly what sct_align reports in those two arrays.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it): it needs no handle and calls no cudaMalloc / cudaFree / allocating routine.  Its device
+ * scratch (the device copy of the reads, the Peq table, the per-read arrays of the pass-1 kernel) is one file-scope static
+ * device array of about 2.6 MB that every GPU loading the library holds until exit.
+ * Limits (SCT_E_UNSUPPORTED beyond them): n <= 8192 reads, read_offsets[n] - read_offsets[0] <= 2 MiB, every read
+ * <= 16384 bases, adapter length <= 32.  Host buffers in, host buffers out, synchronous (legacy default stream).
+ * All calls on one device share the scratch array, which keeps the last call's contents (the call clears what must start
+ * at zero): calls that overlap on one GPU race — serialise them.
+ */
+int sct_align_strand_dist_noalloc(int device, const uint8_t *adapter, int32_t adapter_length, const uint8_t *read_bytes,
+                                  const int64_t *read_offsets, int64_t n, int8_t *strand, int32_t *dist);
+
 /* ---------------------------------------------------------------------------------------------------------------------
  * Native host I/O of the formats either side of the kernels (§8(f) rank 2).  Host code only
  * (threads + zlib); no GPU is needed and nothing here computes a match.

@@ -21,7 +21,7 @@ EXPORTS = (
     "sct_measure_int32_peak", "sct_flush_l2",
     "sct_host_alloc", "sct_host_free", "sct_host_register", "sct_host_unregister", "sct_work_counters", "sct_kernel_name",
     "sct_align_create", "sct_align_destroy", "sct_align", "sct_align_stage", "sct_align_run_staged",
-    "sct_align_stats", "sct_align_set_option",
+    "sct_align_stats", "sct_align_set_option", "sct_align_strand_dist_noalloc",
     "sct_io_read_long_reads", "sct_io_read_fastqs", "sct_io_reads_info", "sct_io_reads_free",
     "sct_io_format_matches", "sct_io_format_lr_bc", "sct_io_buffer_info", "sct_io_buffer_free",
     "sct_io_read_lr_bc_segments", "sct_io_read_whitelist",
@@ -442,6 +442,25 @@ class Aligner:
         s = np.zeros(8, dtype=np.int64)
         _check(lib().sct_align_stats(self._h, _ptr(s, ctypes.c_int64)))
         return dict(zip(ALIGN_STAT_NAMES, s.tolist()))
+
+
+def align_strand_dist_noalloc(adapter: bytes, read_bytes: np.ndarray, offsets: np.ndarray, device: int = 0):
+    """sct_align_strand_dist_noalloc: strand + distance per read without any device allocation (fixed static scratch:
+    <= 8192 reads, <= 2 MiB of bases, reads <= 16384 bases).  -> (strand int8[n], dist int32[n])"""
+    L = lib()
+    L.sct_align_strand_dist_noalloc.restype = ctypes.c_int
+    L.sct_align_strand_dist_noalloc.argtypes = [ctypes.c_int, _u8p, ctypes.c_int32, _u8p, _i64p, ctypes.c_int64,
+                                                ctypes.POINTER(ctypes.c_int8), _i32p]
+    ad = np.frombuffer(bytes(adapter), dtype=np.uint8).copy()
+    rb = _as_u8(read_bytes)
+    off = np.ascontiguousarray(offsets, dtype=np.int64)
+    n = off.shape[0] - 1
+    strand = np.zeros(max(n, 1), dtype=np.int8)
+    dist = np.zeros(max(n, 1), dtype=np.int32)
+    _check(L.sct_align_strand_dist_noalloc(int(device), _ptr(_as_u8(ad), ctypes.c_uint8), int(ad.size), _ptr(rb, ctypes.c_uint8),
+                                           _ptr(off, ctypes.c_int64), n, _ptr(strand, ctypes.c_int8),
+                                           _ptr(dist, ctypes.c_int32)))
+    return strand[:n], dist[:n]
 
 
 def align_reads(adapter: bytes, read_bytes: np.ndarray, offsets: np.ndarray, threads: int = 1, mem_gb: float = 16.0,

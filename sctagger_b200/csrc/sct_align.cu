@@ -501,3 +501,137 @@ int sct_align_run_staged(sct_align_handle *h, float *pass_ms, float *pass1_kerne
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// sct_align_strand_dist_noalloc: pass 1 of the adapter alignment (strand + distance per read) for callers that cannot
+// call cudaMalloc — code under CUDA graph capture, tight serving loops, harnesses that forbid it.  No counterpart in the
+// reference.  Everything pass 1 needs besides the caller's host arrays — the
+// device copy of the reads and offsets, the Peq table, the read order, and the span / work / location-count / list
+// arrays aln_pass1_kernel writes — lives in ONE file-scope static device array of a fixed, modest size (about 2.6 MB,
+// held by every GPU that loads the library until exit).  The entry point calls no cudaMalloc / cudaFree / allocating
+// routine: plain cudaMemcpy / cudaMemset on the legacy default stream and two kernel launches.
+// Every call on a device shares the array and it keeps the last call's contents: the two list counters the kernel bumps
+// are cleared by every call, everything else it reads is rewritten first.  Calls that overlap on one GPU (two host
+// threads) race on it: serialise them.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int64_t NA_MAX_READS = 8192;
+constexpr int64_t NA_MAX_BYTES = 2ll << 20;
+constexpr size_t na_up(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr size_t NA_BYTES = 0;                                                                 // read bytes (+ padding)
+constexpr size_t NA_OFF = NA_BYTES + na_up((size_t)NA_MAX_BYTES + 256);                        // int64[n + 1]
+constexpr size_t NA_PEQ = NA_OFF + na_up((size_t)(NA_MAX_READS + 1) * 8);                      // uint2[256]
+constexpr size_t NA_ORDER = NA_PEQ + na_up(256 * sizeof(uint2));                               // int[n]
+constexpr size_t NA_DIST = NA_ORDER + na_up((size_t)NA_MAX_READS * 4);
+constexpr size_t NA_NLOCS = NA_DIST + na_up((size_t)NA_MAX_READS * 4);
+constexpr size_t NA_WORK = NA_NLOCS + na_up((size_t)NA_MAX_READS * 4);
+constexpr size_t NA_LONG = NA_WORK + na_up((size_t)NA_MAX_READS * 4);
+constexpr size_t NA_SHORT = NA_LONG + na_up((size_t)NA_MAX_READS * 4);
+constexpr size_t NA_SPAN = NA_SHORT + na_up((size_t)NA_MAX_READS * 4);                         // int2[n]
+constexpr size_t NA_STRAND = NA_SPAN + na_up((size_t)NA_MAX_READS * 8);                        // int8[n]
+constexpr size_t NA_CTR = NA_STRAND + na_up((size_t)NA_MAX_READS);                             // n_long, n_short
+constexpr size_t NA_TOTAL = NA_CTR + 256;
+
+}  // namespace
+
+// In host code this name is only a stand-in for the device array (not a device address): cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_TOTAL];
+
+namespace {
+
+__global__ void __launch_bounds__(256) na_iota_kernel(int *order, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) order[i] = i;
+}
+
+constexpr int NA_MAX_DEVICES = 64;
+unsigned char *g_na_base[NA_MAX_DEVICES] = {};      // device address of g_noalloc_scratch, per device
+std::mutex g_na_mutex;
+
+// device address of the scratch array on `device` (which must be current): resolved once per device
+int na_scratch(int device, unsigned char **out) {
+    std::lock_guard<std::mutex> g(g_na_mutex);
+    if (!g_na_base[device]) {
+        void *p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_na_base[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_na_base[device];
+    return SCT_OK;
+}
+
+}  // namespace
+
+extern "C" int sct_align_strand_dist_noalloc(int device, const uint8_t *adapter, int32_t adapter_length, const uint8_t *read_bytes,
+                                             const int64_t *read_offsets, int64_t n, int8_t *strand, int32_t *dist) {
+    if (!adapter || adapter_length < 1) return fail(SCT_E_ARG, "adapter must not be empty");
+    if (adapter_length > 32) return fail(SCT_E_UNSUPPORTED, "adapter length %d > 32 is not implemented", adapter_length);
+    if (n < 0 || !read_offsets || (n > 0 && (!strand || !dist))) return fail(SCT_E_ARG, "bad argument");
+    if (n > NA_MAX_READS)
+        return fail(SCT_E_UNSUPPORTED, "sct_align_strand_dist_noalloc: %lld reads exceed the fixed scratch (at most %lld reads per call)",
+                    (long long)n, (long long)NA_MAX_READS);
+    const int64_t b0 = read_offsets[0], nbytes = read_offsets[n] - b0;
+    if (nbytes < 0) return fail(SCT_E_ARG, "read_offsets must be non-decreasing");
+    if (nbytes > NA_MAX_BYTES)
+        return fail(SCT_E_UNSUPPORTED, "sct_align_strand_dist_noalloc: %lld read bytes exceed the fixed scratch (at most %lld bytes per call)",
+                    (long long)nbytes, (long long)NA_MAX_BYTES);
+    if (nbytes > 0 && !read_bytes) return fail(SCT_E_ARG, "read_bytes is NULL");
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t len = read_offsets[i + 1] - read_offsets[i];
+        if (len < 0) return fail(SCT_E_ARG, "read_offsets must be non-decreasing (read %lld)", (long long)i);
+        if (len > ALN_LONG_READ)
+            return fail(SCT_E_UNSUPPORTED, "sct_align_strand_dist_noalloc: read %lld has %lld bases (at most %d per read)", (long long)i,
+                        (long long)len, ALN_LONG_READ);
+    }
+    const int ndev = sct_device_count();
+    if (ndev == 0) return fail(SCT_E_CUDA, "no CUDA device available (sctagger_b200 has no CPU fallback)");
+    if (device < 0 || device >= ndev || device >= NA_MAX_DEVICES) return fail(SCT_E_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    if (n == 0) return SCT_OK;
+    CUDA_TRY(cudaSetDevice(device));
+    unsigned char *base = nullptr;
+    TRY(na_scratch(device, &base));
+
+    // a1 = adapter, a2 = rev_compl(a1) (scTagger.py:363-365), as in sct_align_create
+    const int m = adapter_length;
+    uint2 peq[256];
+    for (int i = 0; i < 256; ++i) peq[i] = make_uint2(0u, 0u);
+    for (int i = 0; i < m; ++i) {
+        peq[adapter[i]].x |= 1u << i;
+        peq[comp_char(adapter[m - 1 - i])].y |= 1u << i;
+    }
+    CUDA_TRY(cudaMemcpy(base + NA_PEQ, peq, sizeof peq, cudaMemcpyHostToDevice));
+    if (nbytes > 0) CUDA_TRY(cudaMemcpy(base + NA_BYTES, read_bytes + b0, (size_t)nbytes, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(base + NA_OFF, read_offsets, (size_t)(n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemset(base + NA_CTR, 0, 256));            // the list counters start at zero in every call
+
+    AlignParams p;
+    p.bytes = base + NA_BYTES;
+    p.off = reinterpret_cast<const long long *>(base + NA_OFF);
+    p.b0 = b0;
+    p.nbytes = nbytes;
+    p.n = (int)n;
+    p.m = m;
+    p.peq = reinterpret_cast<const uint2 *>(base + NA_PEQ);
+    p.rpeq2 = nullptr;                                       // the start search belongs to pass 2
+    p.order = reinterpret_cast<int *>(base + NA_ORDER);
+    p.strand = reinterpret_cast<signed char *>(base + NA_STRAND);
+    p.dist = reinterpret_cast<int *>(base + NA_DIST);
+    p.n_locs = reinterpret_cast<int *>(base + NA_NLOCS);
+    p.span = reinterpret_cast<int2 *>(base + NA_SPAN);
+    p.work = reinterpret_cast<int *>(base + NA_WORK);
+    p.long_list = reinterpret_cast<int *>(base + NA_LONG);
+    p.n_long = reinterpret_cast<unsigned int *>(base + NA_CTR);
+    p.short_list = reinterpret_cast<int *>(base + NA_SHORT);
+    p.n_short = reinterpret_cast<unsigned int *>(base + NA_CTR) + 1;
+    p.long_cnt = nullptr;
+    p.loc_off = nullptr;
+    p.locs = nullptr;
+    p.loc_cap = 0;
+    na_iota_kernel<<<(unsigned)((n + 255) / 256), 256>>>(reinterpret_cast<int *>(base + NA_ORDER), (int)n);
+    aln_pass1_kernel<<<(unsigned)((n + ALN_THREADS - 1) / ALN_THREADS), ALN_THREADS>>>(p);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpy(strand, base + NA_STRAND, (size_t)n, cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(dist, base + NA_DIST, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost));
+    return SCT_OK;
+}
