@@ -3,7 +3,7 @@
 # ncu summaries of the final kernels.  Outputs land in gpurun_out/ and are copied into profiles/ by hand.
 set -u
 mkdir -p gpurun_out
-(python -m pytest tests -m gpu -x -q 2>&1 | tail -3) > gpurun_out/final_tests.log
+(python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -3) > gpurun_out/final_tests_alone.log; (python -m pytest tests -m gpu -x -q 2>&1 | tail -3) > gpurun_out/final_tests.log
 python bench.py > gpurun_out/final_bench.json 2> gpurun_out/final_bench.err
 python bench.py --impl reference > gpurun_out/final_bench_ref.json 2> gpurun_out/final_bench_ref.err
 python tools/cli_e2e.py 10000000 2 1 > gpurun_out/final_cli_10M.json 2> gpurun_out/final_cli_10M.err
@@ -15,4 +15,4 @@ for k in 2 3; do
 done
 ncu --metrics gpu__time_duration.sum --clock-control none -c 120 --csv --log-file gpurun_out/final_launches_bench.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu --no-secondary > gpurun_out/final_ncu_launches.log 2>&1
-cat gpurun_out/final_tests.log
+cat gpurun_out/final_tests_alone.log gpurun_out/final_tests.log
