@@ -382,6 +382,39 @@ def test_pinned_buffers_zero_copy_path_equals_staged_path():
         x.close()
 
 
+def test_one_handle_growing_calls_stage_then_match_and_chunk_shapes():
+    """One handle across calls of different sizes and kinds: the slots are sized by the call's full chunks (and regrown by
+    a larger call), pinned staging appears only when a pageable call needs it, the resident-batch API in between leaves
+    sct_match intact, and the shapes of the streamed chunks (first / full / last) never change the result."""
+    rng = np.random.default_rng(57)
+    bc, sb, off = util.random_case(rng, 400, 30_000, bl=16, dirty=0.05, max_len=50)
+    want = util.result_from_tuple(oracle.match(bc, sb, off, 2, threads=16, algo="dp"))
+
+    def sub(w, lo, hi):
+        return (w.min_ed[lo:hi], w.n_ties[lo:hi], w.tie_offsets[lo:hi + 1] - w.tie_offsets[lo],
+                w.tie_ids[w.tie_offsets[lo]:w.tie_offsets[hi]])
+
+    def check(res, lo, hi):
+        for x, y in zip((res.min_ed, res.n_ties, res.tie_offsets, res.tie_ids), sub(want, lo, hi)):
+            assert np.array_equal(x, y)
+
+    psb, poff = _lib.Pinned.copy_of(sb), _lib.Pinned.copy_of(off)
+    out = _lib.ResultBuffers(30_000)
+    with _lib.Matcher(bc, 2, 16, stream_segments=4096, ramp_segments=512, tail_segments=300) as m:
+        check(m.match(psb.array, poff.array[:2_001], out=out, copy_ties=False), 0, 2_000)      # small, all page-locked
+        m.stage(sb[:off[5_000]], off[:5_001])                                                  # resident batch in between
+        m.run_staged()
+        check(m.fetch_staged(), 0, 5_000)
+        check(m.match(sb, off), 0, 30_000)                                                     # larger, pageable: slots and staging grow
+        check(m.match(psb.array, poff.array, out=out, copy_ties=False), 0, 30_000)
+        check(m.match(sb, off[10_000:10_700]), 10_000, 10_699)                                 # smaller again, a sub-range
+    for tail in (0, 1, 64, 5_000, 100_000):
+        with _lib.Matcher(bc, 2, 16, stream_segments=8192, ramp_segments=1024, tail_segments=tail) as m:
+            check(m.match(sb, off), 0, 30_000)
+    for x in (psb, poff, out):
+        x.close()
+
+
 @pytest.mark.skipif(_lib.device_count() < 2, reason="needs two GPUs (gpurun --gpus 2)")
 def test_reads_sharded_over_two_gpus_equal_one_gpu():
     """The product's own multi-GPU path (MatcherGroup: one handle + one host thread per GPU, contiguous read ranges,
