@@ -106,6 +106,10 @@ int sct_stats(sct_handle *h, int64_t stats[8]);
  *   "stream_segments", "ramp_segments"    segments per streamed chunk of sct_match, and of its first chunk (the size
  *                                         quadruples from chunk to chunk up to stream_segments so the pipeline fills fast)
  *   "chain_kernels"                       1 (default) = a chunk's kernels start behind the previous chunk's match kernel
+ *   "tail_segments"                       size of the last streamed chunk of a call (default 65536; 0 = no small last chunk)
+ *   "reserve_segments"                    allocate the streaming slots now, for chunks of up to this many segments from
+ *                                         pageable caller arrays, instead of inside the first sct_match (the CLI does it
+ *                                         while it parses the -lr file)
  *   "seed_ctas_per_sm"                    resident CTAs per SM of the seeded kernel (grid = SMs x this)
  *   "seed_deepening"                      1 (default) = search error bounds 1, 2, .. max_error in turn and stop at the first
  *                                         bound with a hit (only the minimum distance and its ties are reported);

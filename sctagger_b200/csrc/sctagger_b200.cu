@@ -801,6 +801,15 @@ int sct_set_option(sct_handle *h, const char *key, int64_t value) {
     } else if (k == "ramp_segments") {
         if (value < 1) return fail(SCT_E_ARG, "ramp_segments must be >= 1");
         h->ramp_segs = value;
+    } else if (k == "reserve_segments") {
+        // allocate the streaming slots now (device buffers and the pinned staging of pageable caller arrays) for chunks of
+        // up to `value` segments, instead of inside the first sct_match: the CLI does this while it parses the -lr file
+        if (value < 1) return fail(SCT_E_ARG, "reserve_segments must be >= 1");
+        CUDA_TRY(cudaSetDevice(h->device));
+        const int64_t segs = std::min<int64_t>(value, h->stream_segs);
+        const int64_t bytes = std::min<int64_t>(h->chunk_bytes, segs * 32 + 4096);
+        h->in_bytes_pinned = h->in_off_pinned = h->out_min_pinned = h->out_nt_pinned = h->out_toff_pinned = false;
+        for (Slot &s : h->slot) TRY(ensure_slot(h, s, segs, bytes));
     } else if (k == "tail_segments") {
         if (value < 0) return fail(SCT_E_ARG, "tail_segments must be >= 0");
         h->tail_segs = value;

@@ -184,7 +184,7 @@ def _match_trie_result(args):
     def make_group():
         try:
             box["group"] = _lib.MatcherGroup(barcode_matrix(barcodes, args.barcode_length), args.max_error, args.threads,
-                                             args.mem, getattr(args, "devices", None))
+                                             args.mem, getattr(args, "devices", None), reserve_segments=1 << 20)
         except Exception as e:
             box["error"] = e
 
