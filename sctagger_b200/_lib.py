@@ -761,14 +761,15 @@ class Whitelist:
     def __exit__(self, *exc):
         self.close()
 
-    def count(self, seg_bytes: np.ndarray, offsets: np.ndarray, per_segment: bool = False):
-        """Adds one batch of segments to the counts; per_segment=True -> (n_hits int32[n], hit_word int32[n])."""
+    def count(self, seg_bytes: np.ndarray, offsets: np.ndarray, per_segment: bool = False, out=None):
+        """Adds one batch of segments to the counts; per_segment=True -> (n_hits int32[n], hit_word int32[n]), written
+        into `out` = (n_hits, hit_word) when given.  Arrays in page-locked memory (`Pinned`) are copied from / to
+        directly; pageable ones are staged by the library's host threads."""
         sb = _as_u8(seg_bytes)
         off = np.ascontiguousarray(offsets, dtype=np.int64)
         n = off.shape[0] - 1
         if per_segment:
-            nh = np.empty(max(n, 1), dtype=np.int32)
-            hw = np.empty(max(n, 1), dtype=np.int32)
+            nh, hw = out if out is not None else (np.empty(max(n, 1), dtype=np.int32), np.empty(max(n, 1), dtype=np.int32))
             _check(lib().sct_wl_count(self._h, _ptr(sb, ctypes.c_uint8), _ptr(off, ctypes.c_int64), n,
                                       _ptr(nh, ctypes.c_int32), _ptr(hw, ctypes.c_int32)))
             return nh[:n], hw[:n]

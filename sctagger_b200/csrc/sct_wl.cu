@@ -21,6 +21,8 @@ struct WSlot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int64_t n = 0, first = 0;
+    long long b0 = 0;                       // offset of the chunk's first byte in the caller's numbering
+    int *dst_hits = nullptr, *dst_word = nullptr;   // the caller's arrays when they are page-locked, else the staging
     bool busy = false;
 };
 
@@ -34,6 +36,9 @@ struct sct_wl_handle {
     int *d_odd_idx = nullptr, *d_odd_off = nullptr;
     unsigned int *d_counts = nullptr;
     unsigned long long *d_first = nullptr;
+    WlSeen *d_seen = nullptr;               // sct_wl_result: compacted (first segment, word, count) of the counted words
+    unsigned long long *d_nseen = nullptr;
+    int64_t seen_cap = 0;
     int64_t chunk_segs = (int64_t)1 << 21, chunk_bytes = (int64_t)64 << 20;
     int64_t next_rid = 0;
     HostPool *pool = nullptr;
@@ -90,6 +95,7 @@ int launch_count(sct_wl_handle *h, WSlot &s, bool per_segment) {
     WlCountParams p;
     p.bytes = s.d_bytes;
     p.off = s.d_off;
+    p.b0 = s.b0;
     p.n = s.n;
     p.first_rid = s.first;
     p.n_hits = per_segment ? s.d_hits : nullptr;
@@ -135,6 +141,8 @@ int sct_wl_destroy(sct_wl_handle *h) {
     dev_free(h->d_odd_off);
     dev_free(h->d_counts);
     dev_free(h->d_first);
+    dev_free(h->d_seen);
+    dev_free(h->d_nseen);
     delete h->pool;
     delete h;
     return SCT_OK;
@@ -299,8 +307,8 @@ static int wl_finish_slot(sct_wl_handle *h, WSlot &s, int32_t *n_hits, int32_t *
     if (!s.busy) return SCT_OK;
     CUDA_TRY(cudaStreamSynchronize(s.stream));
     s.busy = false;
-    if (n_hits && s.n > 0) memcpy(n_hits + s.first, s.h_hits, (size_t)s.n * sizeof(int));
-    if (hit_word && s.n > 0) memcpy(hit_word + s.first, s.h_word, (size_t)s.n * sizeof(int));
+    if (n_hits && s.n > 0 && s.dst_hits == s.h_hits) par_memcpy(h->pool, n_hits + s.first, s.h_hits, (size_t)s.n * sizeof(int));
+    if (hit_word && s.n > 0 && s.dst_word == s.h_word) par_memcpy(h->pool, hit_word + s.first, s.h_word, (size_t)s.n * sizeof(int));
     return SCT_OK;
 }
 
@@ -310,6 +318,11 @@ int sct_wl_count(sct_wl_handle *h, const uint8_t *seg_bytes, const int64_t *seg_
     if (n < 0 || (n > 0 && (!seg_bytes || !seg_offsets))) return fail(SCT_E_ARG, "sct_wl_count: bad arguments");
     CUDA_TRY(cudaSetDevice(h->device));
     const bool per_seg = n_hits || hit_word;
+    const int64_t all_bytes = n > 0 ? seg_offsets[n] - seg_offsets[0] : 0;
+    const bool bytes_pinned = all_bytes > 0 && is_pinned(seg_bytes + seg_offsets[0], (size_t)all_bytes);
+    const bool off_pinned = n > 0 && is_pinned(seg_offsets, (size_t)(n + 1) * sizeof(int64_t));
+    const bool hits_pinned = n > 0 && n_hits && is_pinned(n_hits, (size_t)n * sizeof(int32_t));
+    const bool word_pinned = n > 0 && hit_word && is_pinned(hit_word, (size_t)n * sizeof(int32_t));
     const int64_t rid0 = h->next_rid;
     h->staged = false;
     h->stats[2] = h->stats[3] = h->stats[1] = 0;
@@ -329,27 +342,40 @@ int sct_wl_count(sct_wl_handle *h, const uint8_t *seg_bytes, const int64_t *seg_
         const int64_t cn = b - a, cb = seg_offsets[b] - base;
         if (cb < 0) return fail(SCT_E_ARG, "sct_wl_count: offsets must be non-decreasing");
         TRY(ensure_wslot(s, cn, cb));
-        par_memcpy(h->pool, s.h_bytes, seg_bytes + base, (size_t)cb);
-        bool bad = false;
-        par_ranges(h->pool, cn + 1, 1 << 16, [&](int64_t x, int64_t y) {
-            for (int64_t i = x; i < y; ++i) {
-                s.h_off[i] = seg_offsets[a + i] - base;
-                if (i > 0 && seg_offsets[a + i] < seg_offsets[a + i - 1]) bad = true;
-            }
+        // page-locked caller arrays are copied from / to directly (as in sct_match); the offsets travel in the caller's
+        // numbering (the kernel subtracts the chunk's first offset) and are only READ here, to validate them
+        std::atomic<bool> bad(false);
+        par_ranges(h->pool, cn, 1 << 16, [&](int64_t x, int64_t y) {
+            bool mine = false;
+            for (int64_t i = x; i < y; ++i) mine |= seg_offsets[a + i + 1] < seg_offsets[a + i];
+            if (mine) bad = true;
         });
         if (bad) return fail(SCT_E_ARG, "sct_wl_count: offsets must be non-decreasing");
+        const uint8_t *src_bytes = seg_bytes + base;
+        const long long *src_off = reinterpret_cast<const long long *>(seg_offsets + a);
+        if (!bytes_pinned && cb > 0) {
+            par_memcpy(h->pool, s.h_bytes, src_bytes, (size_t)cb);
+            src_bytes = s.h_bytes;
+        }
+        if (!off_pinned) {
+            par_memcpy(h->pool, s.h_off, src_off, (size_t)(cn + 1) * sizeof(long long));
+            src_off = s.h_off;
+        }
         s.n = cn;
         s.first = a;
-        CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)cb, cudaMemcpyHostToDevice, s.stream));
-        CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(cn + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
+        s.b0 = base;
+        s.dst_hits = hits_pinned ? n_hits + a : s.h_hits;
+        s.dst_word = word_pinned ? hit_word + a : s.h_word;
+        if (cb > 0) CUDA_TRY(cudaMemcpyAsync(s.d_bytes, src_bytes, (size_t)cb, cudaMemcpyHostToDevice, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(s.d_off, src_off, (size_t)(cn + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
         // first_rid of the kernel = job-wide index; s.first stays call-relative for the un-staging
         const int64_t keep = s.first;
         s.first = rid0 + a;
         TRY(launch_count(h, s, per_seg));
         s.first = keep;
         if (per_seg) {
-            CUDA_TRY(cudaMemcpyAsync(s.h_hits, s.d_hits, (size_t)cn * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-            CUDA_TRY(cudaMemcpyAsync(s.h_word, s.d_word, (size_t)cn * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(s.dst_hits, s.d_hits, (size_t)cn * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(s.dst_word, s.d_word, (size_t)cn * sizeof(int), cudaMemcpyDeviceToHost, s.stream));
             h->stats[3] += cn * 8;
         }
         s.busy = true;
@@ -369,22 +395,41 @@ int sct_wl_result(sct_wl_handle *h, int64_t *n_unique, const int32_t **word_idx,
     if (!h || !n_unique || !word_idx || !count) return fail(SCT_E_ARG, "sct_wl_result: null argument");
     CUDA_TRY(cudaSetDevice(h->device));
     try {
-        std::vector<unsigned int> c((size_t)std::max<int64_t>(1, h->n_words));
-        std::vector<unsigned long long> f((size_t)std::max<int64_t>(1, h->n_words));
+        std::vector<WlSeen> seen;
         if (h->n_words > 0) {
-            CUDA_TRY(cudaMemcpy(c.data(), h->d_counts, (size_t)h->n_words * sizeof(unsigned int), cudaMemcpyDeviceToHost));
-            CUDA_TRY(cudaMemcpy(f.data(), h->d_first, (size_t)h->n_words * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-            h->stats[3] += h->n_words * 12;
+            if (!h->d_nseen) CUDA_TRY(cudaMalloc(&h->d_nseen, sizeof(unsigned long long)));
+            unsigned long long n_seen = 0;
+            for (int attempt = 0; attempt < 2; ++attempt) {
+                if (h->seen_cap == 0) {
+                    const int64_t cap = std::min<int64_t>(h->n_words, (int64_t)1 << 18);
+                    CUDA_TRY(cudaMalloc(&h->d_seen, (size_t)cap * sizeof(WlSeen)));
+                    h->seen_cap = cap;
+                }
+                CUDA_TRY(cudaMemset(h->d_nseen, 0, sizeof(unsigned long long)));
+                const int grid = (int)std::min<int64_t>((h->n_words + 255) / 256, (int64_t)h->sm_count * 16);
+                wl_compact_kernel<<<grid, 256>>>(h->d_counts, h->d_first, h->n_words, h->d_seen, (unsigned long long)h->seen_cap, h->d_nseen);
+                CUDA_TRY(cudaGetLastError());
+                CUDA_TRY(cudaMemcpy(&n_seen, h->d_nseen, sizeof n_seen, cudaMemcpyDeviceToHost));
+                h->stats[0] += 1;
+                if ((int64_t)n_seen <= h->seen_cap) break;
+                dev_free(h->d_seen);                       // more counted words than the buffer holds: once more, at size
+                h->seen_cap = 0;
+                CUDA_TRY(cudaMalloc(&h->d_seen, (size_t)n_seen * sizeof(WlSeen)));
+                h->seen_cap = (int64_t)n_seen;
+            }
+            seen.resize((size_t)n_seen);
+            if (n_seen) CUDA_TRY(cudaMemcpy(seen.data(), h->d_seen, (size_t)n_seen * sizeof(WlSeen), cudaMemcpyDeviceToHost));
+            h->stats[3] += (int64_t)n_seen * (int64_t)sizeof(WlSeen) + 8;
         }
-        std::vector<std::pair<unsigned long long, int32_t>> seen;
-        for (int64_t w = 0; w < h->n_words; ++w)
-            if (c[(size_t)w]) seen.emplace_back(f[(size_t)w], (int32_t)w);
-        std::sort(seen.begin(), seen.end());                 // Counter insertion order = first segment that counted it
+        // Counter insertion order = first segment that counted the word (ties cannot occur: a segment counts one word)
+        std::sort(seen.begin(), seen.end(), [](const WlSeen &x, const WlSeen &y) {
+            return x.first != y.first ? x.first < y.first : x.word < y.word;
+        });
         h->res_idx.resize(seen.size());
         h->res_cnt.resize(seen.size());
         for (size_t i = 0; i < seen.size(); ++i) {
-            h->res_idx[i] = seen[i].second;
-            h->res_cnt[i] = c[(size_t)seen[i].second];
+            h->res_idx[i] = seen[i].word;
+            h->res_cnt[i] = seen[i].count;
         }
     } catch (const std::bad_alloc &) {
         return fail(SCT_E_NOMEM, "out of host memory collecting the counts");
@@ -412,6 +457,7 @@ int sct_wl_stage(sct_wl_handle *h, const uint8_t *seg_bytes, const int64_t *seg_
     for (int64_t i = 0; i <= n; ++i) s.h_off[i] = seg_offsets[i] - base;
     s.n = n;
     s.first = 0;
+    s.b0 = 0;                                   // the staged offsets are chunk-relative
     CUDA_TRY(cudaMemcpyAsync(s.d_bytes, s.h_bytes, (size_t)cb, cudaMemcpyHostToDevice, s.stream));
     CUDA_TRY(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * sizeof(long long), cudaMemcpyHostToDevice, s.stream));
     CUDA_TRY(cudaStreamSynchronize(s.stream));

@@ -96,7 +96,8 @@ __device__ __forceinline__ int wl_probe(const WlTable &t, unsigned long long key
 
 struct WlCountParams {
     const uint8_t *bytes;                 // concatenated segments of the chunk
-    const long long *off;                 // n + 1 offsets into bytes
+    const long long *off;                 // n + 1 offsets in the CALLER's numbering: byte j of the chunk is offset b0 + j
+    long long b0;
     long long n;
     long long first_rid;                  // index of segment 0 of the chunk in the whole job (first-seen order)
     int *n_hits;                          // per segment: occurrences of whitelist words (nullable)
@@ -112,8 +113,8 @@ struct WlCountParams {
 __global__ void __launch_bounds__(WL_THREADS) wl_count_kernel(WlTable t, WlCountParams p) {
     const unsigned long long kmask = (t.L >= 32) ? ~0ull : ((1ull << (2 * t.L)) - 1ull);
     for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < p.n; r += (long long)gridDim.x * blockDim.x) {
-        const long long o = p.off[r];
-        const int n = (int)(p.off[r + 1] - o);
+        const long long o = p.off[r] - p.b0;
+        const int n = (int)(p.off[r + 1] - p.b0 - o);
         const uint8_t *s = p.bytes + o;
         unsigned long long key = 0;
         int run = 0, hits = 0, first = -1;
@@ -154,6 +155,27 @@ __global__ void __launch_bounds__(WL_THREADS) wl_count_kernel(WlTable t, WlCount
         }
         if (p.n_hits) p.n_hits[r] = hits;
         if (p.hit_word) p.hit_word[r] = first;
+    }
+}
+
+// Counter read-back: the words that were counted at all (a few thousand cells out of millions of whitelist words) are
+// compacted on the device — (first segment that counted it, word index, count) — so that sct_wl_result moves kilobytes
+// instead of 12 bytes per whitelist word.
+struct WlSeen {
+    unsigned long long first;
+    int word;
+    unsigned int count;
+};
+__global__ void __launch_bounds__(256) wl_compact_kernel(const unsigned int *__restrict__ counts,
+                                                         const unsigned long long *__restrict__ first_seen, long long n_words,
+                                                         WlSeen *__restrict__ out, unsigned long long cap,
+                                                         unsigned long long *__restrict__ n_out) {
+    for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (long long)gridDim.x * blockDim.x) {
+        const unsigned int c = counts[w];
+        if (c) {
+            const unsigned long long at = atomicAdd(n_out, 1ull);
+            if (at < cap) out[at] = WlSeen{first_seen[w], (int)w, c};
+        }
     }
 }
 

@@ -180,3 +180,36 @@ def test_semantics_published_by_pyahocorasick():
     assert A.add_word("she", (9, "SHE")) is False
     A.make_automaton()
     assert (6, (9, "SHE")) in list(A.iter("_hershe_")) and (6, (3, "she")) not in list(A.iter("_hershe_"))
+
+
+@pytest.mark.gpu
+def test_page_locked_arrays_and_compacted_result():
+    """sct_wl_count copies from / to page-locked caller arrays directly (offsets in the caller's numbering, a sub-range
+    included) and sct_wl_result reads back only the counted words: same per-segment hits and the same Counter (order
+    included) as with pageable arrays, over several chunks (2.3 M segments > one chunk of 2 Mi) and several calls."""
+    from sctagger_b200 import _lib
+    rng = np.random.default_rng(12)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    words = acgt[rng.integers(0, 4, size=(5000, 16))]
+    n = 2_300_000
+    segs = acgt[rng.integers(0, 4, size=(n, 20))]
+    planted = np.nonzero(rng.random(n) < 0.6)[0]
+    segs[planted, 2:18] = words[rng.integers(0, 3000, size=planted.size)]
+    sb = segs.reshape(-1)
+    so = np.arange(n + 1, dtype=np.int64) * 20
+    wb, wo = words.reshape(-1), np.arange(5001, dtype=np.int64) * 16
+    psb, pso = _lib.Pinned.copy_of(sb), _lib.Pinned.copy_of(so)
+    pnh, phw = _lib.Pinned(n, np.int32), _lib.Pinned(n, np.int32)
+    with _lib.Whitelist(wb, wo, threads=4) as a, _lib.Whitelist(wb, wo, threads=4) as b:
+        nh, hw = a.count(sb, so, per_segment=True)
+        nh2, hw2 = b.count(psb.array, pso.array, per_segment=True, out=(pnh.array, phw.array))
+        assert b.stats()["chunks"] >= 2
+        assert np.array_equal(nh, nh2) and np.array_equal(hw, hw2) and int((nh == 1).sum()) > n // 2
+        for x, y in zip(a.result(), b.result()):
+            assert np.array_equal(x, y)
+        a.count(sb[so[1000]:so[3000]], so[1000:3001] - so[1000])      # a second call: the job-wide first-seen order goes on
+        b.count(psb.array, pso.array[1000:3001])                      # the same range as a view of the pinned arrays
+        ra, rb = a.result(), b.result()
+        assert np.array_equal(ra[0], rb[0]) and np.array_equal(ra[1], rb[1]) and ra[0].size > 2000
+    for x in (psb, pso, pnh, phw):
+        x.close()

@@ -53,8 +53,24 @@ for _ in range(3):
     idx, cnt = wl.result()
 e2e = (time.perf_counter() - t0) / 3
 st = wl.stats()
-out["e2e"] = {"s": e2e, "segments_per_s": n / e2e, "h2d_bytes": st["h2d_bytes"], "unique_barcodes": int(idx.shape[0]),
-              "counted_segments": int(cnt.sum())}
+out["e2e_pageable"] = {"s": e2e, "segments_per_s": n / e2e, "h2d_bytes": st["h2d_bytes"], "unique_barcodes": int(idx.shape[0]),
+                       "counted_segments": int(cnt.sum())}
+# the same calls on page-locked host arrays (sct_host_alloc): copied from directly, no staging pass
+psb, pso = _lib.Pinned.copy_of(sb), _lib.Pinned.copy_of(so)
+wl.reset()
+wl.count(psb.array, pso.array)
+t0 = time.perf_counter()
+for _ in range(3):
+    wl.reset()
+    wl.count(psb.array, pso.array)
+    idx2, cnt2 = wl.result()
+e2e = (time.perf_counter() - t0) / 3
+st = wl.stats()
+assert np.array_equal(idx, idx2) and np.array_equal(cnt, cnt2)
+out["e2e"] = {"s": e2e, "segments_per_s": n / e2e, "h2d_bytes": st["h2d_bytes"], "d2h_bytes": st["d2h_bytes"],
+              "unique_barcodes": int(idx2.shape[0]), "counted_segments": int(cnt2.sum()),
+              "api": "Whitelist.reset + count + result on page-locked host arrays"}
+psb.close(); pso.close()
 wl.close()
 # CPU restatement (dictionary lookup per window, one core) on a sample
 sample = 200_000
