@@ -271,8 +271,10 @@ int sct_io_buffer_free(sct_buffer *b);
  *   sct_wl_count    <- the per-segment loop over one batch of segments (HOST buffers; streamed in chunks).  Counts are
  *                      accumulated on the device across calls.  Optional per-segment outputs (may be NULL):
  *                      n_hits[r] = len(hits), hit_word[r] = abs(value) of the first hit or -1.
+ *                      Arrays in page-locked memory (sct_host_alloc / sct_host_register) are copied from / to directly.
  *   sct_wl_result   <- the Counter C in insertion order: barcode indices and counts of every barcode counted so far,
  *                      ordered by the first segment that counted it (library-owned until the next call / destroy).
+ *                      Only the counted words leave the device (compacted there), not one counter per whitelist word.
  *   sct_wl_reset    clears the counts.   sct_wl_stage / sct_wl_run_staged: device-resident timing of one batch.
  *   sct_wl_stats    [0] kernel launches, [1] chunks of the last call, [2] host->device bytes, [3] device->host bytes,
  *                   [4] distinct packed keys in the table, [5] segments so far, [6] table slots, [7] literal (non-ACGT) words.
