@@ -25,6 +25,8 @@ gathered on rank 0, concatenated in read order and compared with rank 0's own si
   cpu_baseline / --impl reference   the CPU port of the reference's trie algorithm (oracle/trie_oracle.c, OpenMP over
              the reference's own prefix tasks, -t = host cores) on a bounded sample of the same input; plus the UNMODIFIED
              reference script (oracle/_ref/scTagger.py via oracle/ref_harness.py) on BASELINE configs[0] when present.
+  weak_scaling  (N > 1 only, after the headline) every rank runs the WHOLE input: the job is N times larger; value / e2e of
+             that run, checked against the single-GPU result on every rank.
   secondary  (N = 1 only, after the headline, outside its timed region) configs[3] shape at -mr 3, 40-base segments,
              1 % segments with an N, and the extract_lr_bc adapter alignment (configs[4] shape) on a 200 k-read batch.
 """
@@ -523,6 +525,44 @@ def _main():
             sharded_ok = bool(whole.equals(single))
             digest = result_digest(whole)
 
+    # ---- weak-scaling reading (N > 1 only; a secondary figure, outside the headline's timed regions): EVERY rank runs
+    # the whole input, i.e. the job is N times larger and a rank's share is what one GPU has at N = 1.  It separates the
+    # per-call constant that limits the strong-scaling e2e (a 25 ms job leaves 3 ms per GPU at N = 8) from any shared
+    # bottleneck of N ranks on one host (PCIe, host memory), which would show here as well.
+    weak = None
+    if world > 1:
+        wsb, woff = (sb_all, off_all) if rank == 0 else synth.make_segments_range(bc, 0, n_all)
+        pw_sb, pw_off, w_out = _lib.Pinned.copy_of(wsb), _lib.Pinned.copy_of(woff), _lib.ResultBuffers(n_all)
+        for _ in range(2):
+            rw = m.match(pw_sb.array, pw_off.array, out=w_out, copy_ties=False)
+        w_steps = max(1, min(a.steps, 5))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(w_steps):
+            rw = m.match(pw_sb.array, pw_off.array, out=w_out, copy_ties=False)
+        barrier()
+        w_e2e_s = max_over_ranks(time.perf_counter() - t0)
+        w_digest = result_digest(rw)
+        m.stage(wsb, woff)
+        m.run_staged()
+        w_ms = 0.0
+        barrier()
+        for _ in range(w_steps):
+            m.flush_l2()
+            w_ms += m.run_staged()[0]
+        barrier()
+        w_ms = max_over_ranks(w_ms)
+        ref = [digest if rank == 0 else None]
+        dist.broadcast_object_list(ref, src=0)
+        w_same = sum_over_ranks(0 if w_digest == ref[0] else 1) == 0
+        weak = {"what": f"every one of the {world} ranks runs the WHOLE {n_all:,}-segment input (job = {world} x the headline's)",
+                "segments_total": n_all * world, "steps": w_steps,
+                "value": n_all * world * w_steps / (w_ms * 1e-3), "ms_per_step": w_ms / w_steps,
+                "e2e": {"value": n_all * world * w_steps / w_e2e_s, "ms_per_step": 1e3 * w_e2e_s / w_steps},
+                "every_rank_equals_the_single_gpu_result": bool(w_same), "unit": UNIT}
+        for x in (pw_sb, pw_off, w_out):
+            x.close()
+
     # ---- roofline of the dominant kernel -------------------------------------------------------------------------
     algo_ops = OPS_PER_COLUMN * 2.0 * a.barcodes * total_len          # lane-ops per launch on this rank
     kern_s = kern_ms * 1e-3 / a.steps
@@ -573,6 +613,8 @@ def _main():
                       "sharded_equals_single_gpu": sharded_ok, "fast_segments_rank0": stats["fast_segments"],
                       "generic_segments_rank0": stats["generic_segments"], "generate_s_rank0": t_gen},
         }
+        if weak is not None:
+            line["weak_scaling"] = weak
         if world == 1 and not a.no_cpu:
             ns = min(CPU_SAMPLE, n)
             v, cores, dt, want = cpu_arm(bc, ns, a.max_error)
