@@ -595,7 +595,10 @@ def _main():
             "clocks": clocks,
             "roofline": {"bound": "int32_alu", "kernel": kernel_name,
                          "achieved": achieved / 1e12, "peak": peak_lop3 / 1e12, "unit": "T lane-op/s",
-                         "frac": achieved / peak_lop3, "traffic": (issued or {}).get("dram_bytes"),
+                         "frac": achieved / peak_lop3,
+                         # DRAM bytes per launch of THIS run: the capture's dram__bytes_read + write, scaled from its batch
+                         "traffic": (issued["dram_bytes"] * n / issued["capture_segments"]
+                                     if issued and issued.get("dram_bytes") else None),
                          "useful": useful, "issued": issued,
                          "note": "frac = ALGORITHMIC lane-ops (14 per Myers column update x 2B x sum(len), no credit taken "
                                  "for skipped work) / kernel time / live LOP3 peak: the seeded kernel scores only index "
