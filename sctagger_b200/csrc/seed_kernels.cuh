@@ -630,17 +630,19 @@ __device__ __forceinline__ void seed_phase(const MatchParams &p, const SeedIndex
                 }
             }
             const unsigned pm = __ballot_sync(FULL, pass);
-            if (pass) q_st(qn + __popc(pm & lt_mask), item);
-            qn += __popc(pm);
-            if (qn >= 32) {
-                __syncwarp();
-                verify(q_ld(lane), true);
-                const uint32_t rest = (32 + lane < qn) ? q_ld(32 + lane) : 0u;
-                __syncwarp();
-                q_st(lane, rest);
-                qn -= 32;
-                n_ver += 32u;
-                __syncwarp();
+            if (pm) {                                                     // warp-uniform: four blocks in ten have no survivor
+                if (pass) q_st(qn + __popc(pm & lt_mask), item);
+                qn += __popc(pm);
+                if (qn >= 32) {
+                    __syncwarp();
+                    verify(q_ld(lane), true);
+                    const uint32_t rest = (32 + lane < qn) ? q_ld(32 + lane) : 0u;
+                    __syncwarp();
+                    q_st(lane, rest);
+                    qn -= 32;
+                    n_ver += 32u;
+                    __syncwarp();
+                }
             }
         }
         __syncwarp();
