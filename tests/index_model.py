@@ -176,3 +176,42 @@ def match_segment_windowed(bc_codes, index, seg, K, kpre):
     if best > K:
         return -1, []
     return best, sorted(ties)
+
+
+# ---- responsible-seed pre-check (seed_precheck in csrc/seed_kernels.cuh, rules set in sct_create) ------------------------
+def precheck_rule(bl, K, q):
+    """-> (go_left, characters read, level tested) for piece q of the error-bound-K index (bl = 16 only), or None."""
+    if bl != 16 or K < 1 or K > 3:
+        return None
+    if K == 1:
+        return (q == 1, 6, 1)
+    if K == 2:
+        return (q >= 1, 6 if q == 2 else 5, 2 if q == 2 else 1)
+    return (q % 2 == 1, 4, 1)
+
+
+def anchored_cost(pat, text):
+    """min over prefixes text[:L] of the edit distance between pat and text[:L] (anchored start, free end in the text)."""
+    prev = list(range(len(text) + 1))                  # pat[:0] against text[:L]: L insertions
+    for i, c in enumerate(pat, 1):
+        cur = [i] + [0] * len(text)
+        for L in range(1, len(text) + 1):
+            cur[L] = min(prev[L - 1] + (c != text[L - 1]), prev[L] + 1, cur[L - 1] + 1)
+        prev = cur
+    return min(prev)
+
+
+def precheck_passes(bc_row, text, bl, K, q, piece, j):
+    """Twin of seed_precheck for one candidate: piece q = (offset, length) of barcode bc_row occurs exactly at text[j:]."""
+    rule = precheck_rule(bl, K, q)
+    if rule is None:
+        return True
+    go_left, need, level = rule
+    o, ln = piece
+    if go_left:
+        pat = [int(c) for c in bc_row[o - need:o]][::-1]           # the barcode characters before the piece, outwards
+        side = list(text[:j])[::-1]
+    else:
+        pat = [int(c) for c in bc_row[o + ln:o + ln + need]]
+        side = list(text[j + ln:])
+    return anchored_cost(pat, side) <= level

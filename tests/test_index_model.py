@@ -55,3 +55,38 @@ def test_windowed_model_equals_oracle_on_long_and_dirty_segments(bl, K, t):
         got = im.match_segment_windowed(codes, index, raw[off[r]:off[r + 1]], K, kpre)
         assert got[0] == want.min_ed[r], r
         assert got[1] == want.ties(r).tolist(), r
+
+
+@pytest.mark.parametrize("K,seed", [(1, 1), (2, 2), (3, 3), (2, 4), (3, 5)])
+def test_responsible_seed_precheck_never_loses_a_match(K, seed):
+    """The anchored pre-checks (K = 1: sibling half; K = 2: priority piece 2 > 1 > 0 with the 5-mers testing their
+    neighbour within one edit; K = 3: sibling 4-mer within one edit) are necessary conditions only for the RESPONSIBLE seed
+    of an alignment: every (barcode, strand) within K edits of a segment must still be reached through at least one of
+    its seed occurrences that passes.  Checked here in plain Python, independent of the CUDA code."""
+    rng = np.random.default_rng(8800 + seed)
+    bc, sb, off = util.random_case(rng, 150, 500, bl=16, dirty=0.0, max_len=31)
+    codes = np.vectorize(im.CODE.get)(bc).astype(np.uint8)
+    pieces, tables = im.build_index(codes, K)
+    raw = sb.tobytes()
+    n_true = n_cand = n_pass = 0
+    for r in range(len(off) - 1):
+        seg = raw[off[r]:off[r + 1]]
+        n = len(seg)
+        if n < 16 - K:
+            continue
+        fwd = [im.CODE[b] for b in seg]
+        for strand, text in ((1, fwd), (0, [3 - c for c in reversed(fwd)])):
+            true, reached = set(), set()
+            for q, ((o, ln), table) in enumerate(zip(pieces, tables)):
+                lo, hi = max(0, o - K), min(n - ln, n - (16 - o) + K)
+                for j in range(lo, hi + 1):
+                    for b in table.get(im.pack(text[j:j + ln]), ()):
+                        n_cand += 1
+                        if im.verify(codes[b], text, K) <= K:
+                            true.add(b)
+                        if im.precheck_passes(codes[b], text, 16, K, q, (o, ln), j):
+                            n_pass += 1
+                            reached.add(b)
+            assert true <= reached, (r, strand, sorted(true - reached))
+            n_true += len(true)
+    assert n_true > 100 and n_pass < n_cand          # many real matches were checked, and the filter does filter
