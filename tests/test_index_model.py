@@ -90,3 +90,41 @@ def test_responsible_seed_precheck_never_loses_a_match(K, seed):
             assert true <= reached, (r, strand, sorted(true - reached))
             n_true += len(true)
     assert n_true > 100 and n_pass < n_cand          # many real matches were checked, and the filter does filter
+
+
+def test_anchored_verification_of_error_bound_1_is_exact():
+    """Phase 1 (pieces 8 + 8) scores a candidate ANCHORED at its seed: the other half, 8 characters outwards from the seed
+    boundary, within 0 or 1 edits (seed_anchor_level1).  Through any seed occurrence that can only over-estimate the
+    barcode's distance, and through the responsible one it is exact: the minimum over a barcode's seed occurrences equals
+    the true distance whenever that is <= 1."""
+    rng = np.random.default_rng(4711)
+    bc, sb, off = util.random_case(rng, 200, 700, bl=16, dirty=0.0, max_len=31)
+    codes = np.vectorize(im.CODE.get)(bc).astype(np.uint8)
+    pieces, tables = im.build_index(codes, 1)
+    assert pieces == [(0, 8), (8, 8)]
+    raw = sb.tobytes()
+    n_checked = 0
+    for r in range(len(off) - 1):
+        seg = raw[off[r]:off[r + 1]]
+        n = len(seg)
+        if n < 15:
+            continue
+        fwd = [im.CODE[b] for b in seg]
+        for text in (fwd, [3 - c for c in reversed(fwd)]):
+            best = {}
+            for q, ((o, ln), table) in enumerate(zip(pieces, tables)):
+                for j in range(max(0, o - 1), min(n - ln, n - (16 - o) + 1) + 1):
+                    for b in table.get(im.pack(text[j:j + ln]), ()):
+                        if q == 0:
+                            lv = im.anchored_cost([int(c) for c in codes[b][8:]], list(text[j + 8:]))
+                        else:
+                            lv = im.anchored_cost([int(c) for c in codes[b][:8]][::-1], list(text[:j])[::-1])
+                        lv = min(lv, 2)
+                        true = im.verify(codes[b], text, 1)
+                        assert lv >= true, (r, b, q, j)                      # never an under-estimate
+                        best[b] = (min(best.get(b, (2, 2))[0], lv), true)
+            for b, (lv, true) in best.items():
+                if true <= 1:
+                    assert lv == true, (r, b)
+                    n_checked += 1
+    assert n_checked > 200
